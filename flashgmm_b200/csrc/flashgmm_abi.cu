@@ -1,0 +1,736 @@
+// flashgmm_abi.cu -- the C ABI declared in include/flashgmm.h: contexts, chunked
+// host<->device pipelines, and the hand-off between the sm_100a kernels
+// (gmm_kernels.cu) and the serial host rANS recurrence (rans_host.hpp).
+//
+// Pipeline shape (one "lane" = 3 slots, one CUDA stream + event per slot):
+//   encode: chunks are issued LAST FIRST (rANS encodes in reverse symbol order):
+//           [H2D params] -> startfreq kernel -> D2H packed words; the host pushes
+//           chunk c while chunks c-1, c-2 are in flight on the other slots.
+//   decode: chunks in forward order: [H2D params] -> cdf-table kernel -> D2H rows;
+//           the host pops chunk c while c+1, c+2 are in flight.
+// Batch calls spread independent streams over the ctx's lanes (one worker thread each).
+#include <atomic>
+#include <algorithm>
+#include <condition_variable>
+#include <cstdarg>
+#include <cstdio>
+#include <functional>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/flashgmm.h"
+#include "gmm_kernels.h"
+#include "rans_host.hpp"
+
+using namespace flashgmm;
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<uint64_t> g_launches{0};
+
+// Optional per-kernel timing (bench.py's live roofline): CUDA events around each
+// launch on the launching stream, read back when the chunk is consumed.
+enum { PROF_STARTFREQ = 0, PROF_TABLE = 1, PROF_KINDS = 2 };
+std::atomic<int> g_prof_on{0};
+std::mutex g_prof_mu;
+double g_prof_ms[PROF_KINDS] = {0, 0};
+double g_prof_bytes[PROF_KINDS] = {0, 0};
+uint64_t g_prof_launches[PROF_KINDS] = {0, 0};
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU_TRY(expr)                                                                          \
+    do {                                                                                      \
+        cudaError_t e__ = (expr);                                                             \
+        if (e__ != cudaSuccess)                                                               \
+            return fail(FLASHGMM_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), \
+                        __FILE__, __LINE__);                                                  \
+    } while (0)
+
+constexpr int kSlots = 3;
+
+long env_long(const char* name, long dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atol(v) : dflt;
+}
+
+// Grow-only device / pinned buffers.
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t need(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 4;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t need(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 4;
+        cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocDefault);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+struct Slot {
+    cudaStream_t st = nullptr;
+    cudaEvent_t ev = nullptr;
+    cudaEvent_t k0 = nullptr, k1 = nullptr;   // kernel timing (profiling only)
+    int prof_kind = -1;
+    double prof_bytes = 0;
+    DevBuf d_in;      // staged symbols + parameters (host-memory callers)
+    DevBuf d_out;     // packed words / table rows
+    PinBuf h_out;     // D2H landing zone
+    PinBuf h_sym;     // lazily fetched symbols (device-memory callers, bypass only)
+};
+
+struct Lane {
+    Slot slot[kSlots];
+    BackBuffer bb;
+    PinBuf h_dec;     // decoded symbols before H2D (device-memory callers)
+    bool ready = false;
+    int init() {
+        if (ready) return FLASHGMM_OK;
+        for (auto& s : slot) {
+            CU_TRY(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
+            CU_TRY(cudaEventCreateWithFlags(&s.ev, cudaEventDisableTiming));
+            CU_TRY(cudaEventCreate(&s.k0));
+            CU_TRY(cudaEventCreate(&s.k1));
+        }
+        ready = true;
+        return FLASHGMM_OK;
+    }
+    void destroy() {
+        for (auto& s : slot) {
+            if (s.st) cudaStreamDestroy(s.st);
+            if (s.ev) cudaEventDestroy(s.ev);
+            if (s.k0) cudaEventDestroy(s.k0);
+            if (s.k1) cudaEventDestroy(s.k1);
+            s.d_in.release(); s.d_out.release(); s.h_out.release(); s.h_sym.release();
+            s.st = nullptr; s.ev = nullptr;
+        }
+        h_dec.release();
+        ready = false;
+    }
+};
+
+// Minimal persistent worker pool: run(fn, count) executes fn(worker_index) on
+// `count` workers and waits.
+class Pool {
+public:
+    explicit Pool(int n) : n_(n) {
+        for (int i = 0; i < n; ++i) th_.emplace_back([this, i] { loop(i); });
+    }
+    ~Pool() {
+        { std::lock_guard<std::mutex> g(m_); stop_ = true; ++gen_; }
+        cv_.notify_all();
+        for (auto& t : th_) t.join();
+    }
+    int size() const { return n_; }
+    void run(const std::function<void(int)>& fn, int count) {
+        std::unique_lock<std::mutex> g(m_);
+        fn_ = &fn; want_ = std::min(count, n_); done_ = 0; ++gen_;
+        cv_.notify_all();
+        cv_done_.wait(g, [this] { return done_ == want_; });
+        fn_ = nullptr;
+    }
+private:
+    void loop(int i) {
+        uint64_t seen = 0;
+        for (;;) {
+            const std::function<void(int)>* fn;
+            {
+                std::unique_lock<std::mutex> g(m_);
+                cv_.wait(g, [&] { return gen_ != seen; });
+                seen = gen_;
+                if (stop_) return;
+                if (i >= want_) continue;
+                fn = fn_;
+            }
+            (*fn)(i);
+            { std::lock_guard<std::mutex> g(m_); ++done_; }
+            cv_done_.notify_one();
+        }
+    }
+    int n_;
+    std::vector<std::thread> th_;
+    std::mutex m_;
+    std::condition_variable cv_, cv_done_;
+    const std::function<void(int)>* fn_ = nullptr;
+    int want_ = 0, done_ = 0;
+    uint64_t gen_ = 0;
+    bool stop_ = false;
+};
+
+}  // namespace
+
+struct flashgmm_ctx {
+    int device = 0;
+    std::mutex mu;
+    std::vector<std::unique_ptr<Lane>> lanes;   // lane 0 = caller's thread; 1.. = workers
+    std::unique_ptr<Pool> pool;
+    int64_t enc_chunk = 1 << 20;
+    int64_t dec_chunk_bytes = 16 << 20;
+    int n_workers = 8;
+};
+
+namespace {
+
+inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+
+inline void prof_begin(Slot& S, int kind, double bytes) {
+    S.prof_kind = -1;
+    if (!g_prof_on.load(std::memory_order_relaxed)) return;
+    if (cudaEventRecord(S.k0, S.st) == cudaSuccess) { S.prof_kind = kind; S.prof_bytes = bytes; }
+}
+inline void prof_end(Slot& S) {
+    if (S.prof_kind >= 0) cudaEventRecord(S.k1, S.st);
+}
+inline void prof_collect(Slot& S) {   // call after the slot's work is known to be complete
+    if (S.prof_kind < 0) return;
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, S.k0, S.k1) == cudaSuccess) {
+        std::lock_guard<std::mutex> g(g_prof_mu);
+        g_prof_ms[S.prof_kind] += ms;
+        g_prof_bytes[S.prof_kind] += S.prof_bytes;
+        g_prof_launches[S.prof_kind] += 1;
+    }
+    S.prof_kind = -1;
+}
+
+int check_gmm_args(const float* sc, const float* mu, const float* w, int64_t n, int64_t sn, int64_t sk,
+                   int mode, int mem) {
+    if (n < 0) return fail(FLASHGMM_EINVAL, "n must be >= 0");
+    if (mode < 0 || mode > 2) return fail(FLASHGMM_EINVAL, "mode must be 0 (Polya), 1 (A&S) or 2 (logistic)");
+    if (mem != FLASHGMM_MEM_HOST && mem != FLASHGMM_MEM_DEVICE) return fail(FLASHGMM_EINVAL, "bad mem kind");
+    if (n > 0 && (!sc || !mu || !w)) return fail(FLASHGMM_EINVAL, "null parameter pointer");
+    if (mem == FLASHGMM_MEM_HOST && n > 0) {
+        bool kmajor = (sn == 1 && sk >= n);
+        bool aos = (sk == 1 && sn == 4);
+        if (!kmajor && !aos)
+            return fail(FLASHGMM_EINVAL,
+                        "host parameters must be K-major planes (stride_n=1, stride_k>=n) or (N,4) "
+                        "row-major (stride_n=4, stride_k=1); got stride_n=%lld stride_k=%lld",
+                        (long long)sn, (long long)sk);
+    }
+    return FLASHGMM_OK;
+}
+
+// Stage parameters (and optionally symbols) of chunk [c0, c0+cnt) from host memory
+// into S.d_in; returns the device view.
+int stage_chunk(Slot& S, const flashgmm_stream& s, int64_t c0, int64_t cnt, bool with_symbols,
+                GmmParamsView* view, const int32_t** sym_d) {
+    const int64_t cntp = round_up(cnt, 4);
+    const size_t plane = (size_t)cntp * 4 * sizeof(float);
+    const size_t sym_bytes = with_symbols ? (size_t)cntp * 4 : 0;
+    CU_TRY(S.d_in.need(sym_bytes + 3 * plane));
+    char* base = static_cast<char*>(S.d_in.p);
+    float* d_sc = reinterpret_cast<float*>(base + sym_bytes);
+    float* d_mu = reinterpret_cast<float*>(base + sym_bytes + plane);
+    float* d_w = reinterpret_cast<float*>(base + sym_bytes + 2 * plane);
+    if (with_symbols) {
+        CU_TRY(cudaMemcpyAsync(base, s.symbols + c0, (size_t)cnt * 4, cudaMemcpyHostToDevice, S.st));
+        *sym_d = reinterpret_cast<const int32_t*>(base);
+    }
+    if (s.stride_n == 1) {   // K-major planes -> [4][cntp]
+        const size_t spitch = (size_t)s.stride_k * 4, dpitch = (size_t)cntp * 4, width = (size_t)cnt * 4;
+        CU_TRY(cudaMemcpy2DAsync(d_sc, dpitch, s.scales + c0, spitch, width, 4, cudaMemcpyHostToDevice, S.st));
+        CU_TRY(cudaMemcpy2DAsync(d_mu, dpitch, s.means + c0, spitch, width, 4, cudaMemcpyHostToDevice, S.st));
+        CU_TRY(cudaMemcpy2DAsync(d_w, dpitch, s.weights + c0, spitch, width, 4, cudaMemcpyHostToDevice, S.st));
+        *view = GmmParamsView{d_sc, d_mu, d_w, 1, cntp};
+    } else {                 // (N,4) row-major
+        const size_t bytes = (size_t)cnt * 16;
+        CU_TRY(cudaMemcpyAsync(d_sc, s.scales + c0 * 4, bytes, cudaMemcpyHostToDevice, S.st));
+        CU_TRY(cudaMemcpyAsync(d_mu, s.means + c0 * 4, bytes, cudaMemcpyHostToDevice, S.st));
+        CU_TRY(cudaMemcpyAsync(d_w, s.weights + c0 * 4, bytes, cudaMemcpyHostToDevice, S.st));
+        *view = GmmParamsView{d_sc, d_mu, d_w, 4, 1};
+    }
+    return FLASHGMM_OK;
+}
+
+inline GmmParamsView device_view(const flashgmm_stream& s, int64_t c0) {
+    return GmmParamsView{s.scales + c0 * s.stride_n, s.means + c0 * s.stride_n,
+                         s.weights + c0 * s.stride_n, s.stride_n, s.stride_k};
+}
+
+// ---------------- encode one stream on one lane ----------------
+int encode_stream(flashgmm_ctx* ctx, Lane& L, flashgmm_stream& s, int mode, int mem) {
+    int rc = check_gmm_args(s.scales, s.means, s.weights, s.n, s.stride_n, s.stride_k, mode, mem);
+    if (rc) return rc;
+    if (s.n > 0 && !s.symbols) return fail(FLASHGMM_EINVAL, "null symbols");
+    if (!s.bytes && s.bytes_cap) return fail(FLASHGMM_EINVAL, "null output buffer");
+    if ((rc = L.init())) return rc;
+
+    const int64_t n = s.n, CH = ctx->enc_chunk;
+    const int64_t nch = (n + CH - 1) / CH;
+    L.bb.reset((size_t)(n * 9 / 16) + 64);
+    RansEncoder64 enc;
+    enc.init(&L.bb);
+
+    auto issue = [&](int64_t q) -> int {
+        const int64_t c = nch - 1 - q, c0 = c * CH, cnt = std::min(CH, n - c0);
+        Slot& S = L.slot[q % kSlots];
+        const int64_t cntp = round_up(cnt, 4);
+        CU_TRY(S.d_out.need((size_t)(cntp + 4) * 4));
+        CU_TRY(S.h_out.need((size_t)(cntp + 4) * 4));
+        uint32_t* d_packed = static_cast<uint32_t*>(S.d_out.p);
+        uint32_t* d_flag = d_packed + cntp;
+        GmmParamsView view;
+        const int32_t* sym_d;
+        if (mem == FLASHGMM_MEM_HOST) {
+            int r = stage_chunk(S, s, c0, cnt, true, &view, &sym_d);
+            if (r) return r;
+        } else {
+            view = device_view(s, c0);
+            sym_d = s.symbols + c0;
+        }
+        CU_TRY(cudaMemsetAsync(d_flag, 0, 4, S.st));
+        prof_begin(S, PROF_STARTFREQ, 56.0 * (double)cnt);
+        CU_TRY(launch_gmm_startfreq(sym_d, view, cnt, mode, d_packed, d_flag, S.st));
+        prof_end(S);
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        CU_TRY(cudaMemcpyAsync(S.h_out.p, d_packed, (size_t)(cntp + 1) * 4, cudaMemcpyDeviceToHost, S.st));
+        CU_TRY(cudaEventRecord(S.ev, S.st));
+        return FLASHGMM_OK;
+    };
+
+    for (int64_t q = 0; q < std::min<int64_t>(kSlots, nch); ++q)
+        if ((rc = issue(q))) return rc;
+    for (int64_t q = 0; q < nch; ++q) {
+        const int64_t c = nch - 1 - q, c0 = c * CH, cnt = std::min(CH, n - c0);
+        Slot& S = L.slot[q % kSlots];
+        CU_TRY(cudaEventSynchronize(S.ev));
+        prof_collect(S);
+        const uint32_t* packed = static_cast<const uint32_t*>(S.h_out.p);
+        const int32_t* sym_h = nullptr;
+        if (mem == FLASHGMM_MEM_HOST) {
+            sym_h = s.symbols + c0;
+        } else if (packed[round_up(cnt, 4)] != 0) {   // chunk has bypass symbols: fetch their values
+            CU_TRY(S.h_sym.need((size_t)cnt * 4));
+            CU_TRY(cudaMemcpyAsync(S.h_sym.p, s.symbols + c0, (size_t)cnt * 4, cudaMemcpyDeviceToHost, S.st));
+            CU_TRY(cudaStreamSynchronize(S.st));
+            sym_h = static_cast<const int32_t*>(S.h_sym.p);
+        }
+        enc.push_chunk_reverse(packed, sym_h, cnt);
+        if (q + kSlots < nch && (rc = issue(q + kSlots))) return rc;
+    }
+    enc.flush();
+    s.bytes_len = L.bb.bytes();
+    if (s.bytes_len > s.bytes_cap)
+        return fail(FLASHGMM_ENOSPC, "output buffer too small: need %zu bytes, have %zu", s.bytes_len, s.bytes_cap);
+    memcpy(s.bytes, L.bb.data(), s.bytes_len);
+    return FLASHGMM_OK;
+}
+
+// ---------------- decode one stream on one lane ----------------
+constexpr int32_t kMaxTableR = 16383;
+
+int decode_stream(flashgmm_ctx* ctx, Lane& L, flashgmm_stream& s, int mode, int mem) {
+    int rc = check_gmm_args(s.scales, s.means, s.weights, s.n, s.stride_n, s.stride_k, mode, mem);
+    if (rc) return rc;
+    if (!s.bytes) return fail(FLASHGMM_EINVAL, "null bitstream");
+    if (s.n > 0 && !s.symbols_out) return fail(FLASHGMM_EINVAL, "null symbols_out");
+    const int32_t R = s.max_bs_value;
+    if (R < 0 || R > kMaxTableR)
+        return fail(FLASHGMM_EINVAL, "max_bs_value %d outside supported search radius [0, %d]", R, kMaxTableR);
+    if ((rc = L.init())) return rc;
+
+    const int64_t n = s.n;
+    const int rs = gmm_table_row_stride(R);
+    int64_t CH = ctx->dec_chunk_bytes / (rs * 2);
+    CH = std::max<int64_t>(1024, std::min<int64_t>(CH, 1 << 20)) / 128 * 128;
+    const int64_t nch = (n + CH - 1) / CH;
+
+    int32_t* out_h = s.symbols_out;
+    if (mem == FLASHGMM_MEM_DEVICE && n > 0) {
+        CU_TRY(L.h_dec.need((size_t)n * 4));
+        out_h = static_cast<int32_t*>(L.h_dec.p);
+    }
+
+    auto issue = [&](int64_t q) -> int {
+        const int64_t c0 = q * CH, cnt = std::min(CH, n - c0);
+        Slot& S = L.slot[q % kSlots];
+        const size_t tab_bytes = (size_t)cnt * rs * 2;
+        CU_TRY(S.d_out.need(tab_bytes));
+        CU_TRY(S.h_out.need(tab_bytes));
+        GmmParamsView view;
+        if (mem == FLASHGMM_MEM_HOST) {
+            const int32_t* unused;
+            int r = stage_chunk(S, s, c0, cnt, false, &view, &unused);
+            if (r) return r;
+        } else {
+            view = device_view(s, c0);
+        }
+        prof_begin(S, PROF_TABLE, (48.0 + 2.0 * rs) * (double)cnt);
+        CU_TRY(launch_gmm_cdf_table(view, cnt, mode, R, static_cast<uint16_t*>(S.d_out.p), rs, S.st));
+        prof_end(S);
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        CU_TRY(cudaMemcpyAsync(S.h_out.p, S.d_out.p, tab_bytes, cudaMemcpyDeviceToHost, S.st));
+        CU_TRY(cudaEventRecord(S.ev, S.st));
+        return FLASHGMM_OK;
+    };
+
+    RansDecoder64 dec;
+    dec.init(s.bytes, s.bytes_cap);
+    for (int64_t q = 0; q < std::min<int64_t>(kSlots, nch); ++q)
+        if ((rc = issue(q))) return rc;
+    for (int64_t q = 0; q < nch; ++q) {
+        const int64_t c0 = q * CH, cnt = std::min(CH, n - c0);
+        Slot& S = L.slot[q % kSlots];
+        CU_TRY(cudaEventSynchronize(S.ev));
+        prof_collect(S);
+        const uint16_t* row = static_cast<const uint16_t*>(S.h_out.p);
+        int32_t* o = out_h + c0;
+        for (int64_t i = 0; i < cnt; ++i, row += rs) {
+            const uint32_t cum = dec.get();
+            int32_t v;
+            if (__builtin_expect(cum == kMaxCdf, 0)) {
+                dec.advance(kMaxCdf, 1);
+                v = (int32_t)dec.bypass_raw();
+            } else {
+                uint32_t st, fr;
+                v = search_row(row, R, cum, &st, &fr);
+                dec.advance(st, fr);
+            }
+            o[i] = v;
+        }
+        if (mem == FLASHGMM_MEM_DEVICE)
+            CU_TRY(cudaMemcpyAsync(s.symbols_out + c0, o, (size_t)cnt * 4, cudaMemcpyHostToDevice, S.st));
+        if (q + kSlots < nch && (rc = issue(q + kSlots))) return rc;
+    }
+    if (mem == FLASHGMM_MEM_DEVICE)
+        for (auto& S : L.slot) CU_TRY(cudaStreamSynchronize(S.st));
+    if (dec.overrun) return fail(FLASHGMM_ETRUNC, "bitstream truncated: decoder read past %zu bytes", s.bytes_cap);
+    return FLASHGMM_OK;
+}
+
+Lane& lane_of(flashgmm_ctx* ctx, int idx) {
+    while ((int)ctx->lanes.size() <= idx) ctx->lanes.emplace_back(new Lane());
+    return *ctx->lanes[idx];
+}
+
+typedef int (*stream_fn)(flashgmm_ctx*, Lane&, flashgmm_stream&, int, int);
+
+int run_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem, stream_fn fn) {
+    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
+    if (n_streams < 0 || (n_streams > 0 && !streams)) return fail(FLASHGMM_EINVAL, "bad stream array");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CU_TRY(cudaSetDevice(ctx->device));
+    if (n_streams <= 1 || ctx->n_workers <= 1) {
+        int worst = FLASHGMM_OK;
+        for (int i = 0; i < n_streams; ++i) {
+            streams[i].status = fn(ctx, lane_of(ctx, 0), streams[i], mode, mem);
+            if (streams[i].status) worst = streams[i].status;
+        }
+        return worst;
+    }
+    // longest stream first, dealt to whichever worker is free
+    std::vector<int> order(n_streams);
+    for (int i = 0; i < n_streams; ++i) order[i] = i;
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return streams[a].n > streams[b].n; });
+    if (!ctx->pool) ctx->pool.reset(new Pool(ctx->n_workers));
+    const int nw = std::min(ctx->n_workers, n_streams);
+    for (int i = 0; i < nw; ++i) lane_of(ctx, i + 1);
+    std::atomic<int> next{0};
+    std::vector<std::string> errs(nw);
+    std::function<void(int)> work = [&](int wi) {
+        cudaSetDevice(ctx->device);
+        Lane& L = *ctx->lanes[wi + 1];
+        for (;;) {
+            int k = next.fetch_add(1);
+            if (k >= n_streams) break;
+            flashgmm_stream& s = streams[order[k]];
+            s.status = fn(ctx, L, s, mode, mem);
+            if (s.status) errs[wi] = g_err;
+        }
+    };
+    ctx->pool->run(work, nw);
+    int worst = FLASHGMM_OK;
+    for (int i = 0; i < n_streams; ++i) if (streams[i].status) worst = streams[i].status;
+    if (worst) for (auto& e : errs) if (!e.empty()) { g_err = e; break; }
+    return worst;
+}
+
+}  // namespace
+
+// ============================ extern "C" surface ============================
+extern "C" {
+
+int flashgmm_version(void) { return 100; }
+
+const char* flashgmm_last_error(void) { return g_err.c_str(); }
+
+uint64_t flashgmm_launch_count(void) { return g_launches.load(); }
+
+void flashgmm_profile_enable(int on) { g_prof_on.store(on ? 1 : 0); }
+
+void flashgmm_profile_reset(void) {
+    std::lock_guard<std::mutex> g(g_prof_mu);
+    for (int k = 0; k < PROF_KINDS; ++k) { g_prof_ms[k] = 0; g_prof_bytes[k] = 0; g_prof_launches[k] = 0; }
+}
+
+int flashgmm_profile_read(int kind, double* total_ms, uint64_t* launches, double* algorithmic_bytes) {
+    if (kind < 0 || kind >= PROF_KINDS) return fail(FLASHGMM_EINVAL, "kind must be 0 (startfreq) or 1 (cdf_table)");
+    std::lock_guard<std::mutex> g(g_prof_mu);
+    if (total_ms) *total_ms = g_prof_ms[kind];
+    if (launches) *launches = g_prof_launches[kind];
+    if (algorithmic_bytes) *algorithmic_bytes = g_prof_bytes[kind];
+    return FLASHGMM_OK;
+}
+
+size_t flashgmm_max_encoded_bytes(int64_t n) {
+    if (n < 0) n = 0;
+    return (size_t)4 * ((size_t)10 * (size_t)n + 16);
+}
+
+int flashgmm_ctx_create(int device, flashgmm_ctx** out) {
+    if (!out) return fail(FLASHGMM_EINVAL, "null out pointer");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(FLASHGMM_ECUDA, "no CUDA device available (%s); flashgmm_b200 has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    if (device < 0 || device >= count) return fail(FLASHGMM_EINVAL, "device %d out of range [0,%d)", device, count);
+    CU_TRY(cudaSetDevice(device));
+    CU_TRY(cudaFree(0));
+    flashgmm_ctx* c = new flashgmm_ctx();
+    c->device = device;
+    c->enc_chunk = std::max<long>(4096, env_long("FLASHGMM_ENC_CHUNK", 1 << 20)) / 4 * 4;
+    c->dec_chunk_bytes = std::max<long>(1 << 16, env_long("FLASHGMM_DEC_CHUNK_BYTES", 16 << 20));
+    long hw = (long)std::thread::hardware_concurrency();
+    c->n_workers = (int)std::max<long>(1, env_long("FLASHGMM_WORKERS", std::min<long>(16, hw > 1 ? hw - 1 : 1)));
+    rcp_table();
+    *out = c;
+    return FLASHGMM_OK;
+}
+
+void flashgmm_ctx_destroy(flashgmm_ctx* ctx) {
+    if (!ctx) return;
+    ctx->pool.reset();
+    cudaSetDevice(ctx->device);
+    for (auto& l : ctx->lanes) l->destroy();
+    delete ctx;
+}
+
+int flashgmm_gmm_startfreq(flashgmm_ctx* ctx, const int32_t* symbols_d, const float* scales_d,
+                           const float* means_d, const float* weights_d, int64_t n, int64_t stride_n,
+                           int64_t stride_k, int mode, uint32_t* packed_out_d, void* stream) {
+    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
+    int rc = check_gmm_args(scales_d, means_d, weights_d, n, stride_n, stride_k, mode, FLASHGMM_MEM_DEVICE);
+    if (rc) return rc;
+    if (n > 0 && (!symbols_d || !packed_out_d)) return fail(FLASHGMM_EINVAL, "null symbols / output");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CU_TRY(cudaSetDevice(ctx->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    Lane& L = lane_of(ctx, 0);
+    if (!st) { if ((rc = L.init())) return rc; st = L.slot[0].st; }
+    GmmParamsView v{scales_d, means_d, weights_d, stride_n, stride_k};
+    CU_TRY(launch_gmm_startfreq(symbols_d, v, n, mode, packed_out_d, nullptr, st));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (!stream) CU_TRY(cudaStreamSynchronize(st));
+    return FLASHGMM_OK;
+}
+
+int flashgmm_gmm_table_row_stride(int32_t R) { return R < 0 ? -1 : gmm_table_row_stride(R); }
+
+int flashgmm_gmm_cdf_table(flashgmm_ctx* ctx, const float* scales_d, const float* means_d,
+                           const float* weights_d, int64_t n, int64_t stride_n, int64_t stride_k,
+                           int mode, int32_t R, uint16_t* table_d, int64_t row_stride, void* stream) {
+    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
+    int rc = check_gmm_args(scales_d, means_d, weights_d, n, stride_n, stride_k, mode, FLASHGMM_MEM_DEVICE);
+    if (rc) return rc;
+    if (R < 0 || R > kMaxTableR) return fail(FLASHGMM_EINVAL, "R outside [0, %d]", kMaxTableR);
+    if (row_stride != gmm_table_row_stride(R))
+        return fail(FLASHGMM_EINVAL, "row_stride must be flashgmm_gmm_table_row_stride(R) = %d", gmm_table_row_stride(R));
+    if (n > 0 && !table_d) return fail(FLASHGMM_EINVAL, "null table");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CU_TRY(cudaSetDevice(ctx->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    Lane& L = lane_of(ctx, 0);
+    if (!st) { if ((rc = L.init())) return rc; st = L.slot[0].st; }
+    GmmParamsView v{scales_d, means_d, weights_d, stride_n, stride_k};
+    CU_TRY(launch_gmm_cdf_table(v, n, mode, R, table_d, (int)row_stride, st));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (!stream) CU_TRY(cudaStreamSynchronize(st));
+    return FLASHGMM_OK;
+}
+
+int flashgmm_gmm_encode(flashgmm_ctx* ctx, const int32_t* symbols, const float* scales,
+                        const float* means, const float* weights, int64_t n, int64_t stride_n,
+                        int64_t stride_k, int mode, int mem, uint8_t* out, size_t out_cap,
+                        size_t* out_len) {
+    if (!out_len) return fail(FLASHGMM_EINVAL, "null out_len");
+    flashgmm_stream s{};
+    s.symbols = symbols; s.scales = scales; s.means = means; s.weights = weights;
+    s.n = n; s.stride_n = stride_n; s.stride_k = stride_k;
+    s.bytes = out; s.bytes_cap = out_cap;
+    int rc = run_batch(ctx, &s, 1, mode, mem, encode_stream);
+    *out_len = s.bytes_len;
+    return rc;
+}
+
+int flashgmm_gmm_decode(flashgmm_ctx* ctx, const uint8_t* encoded, size_t encoded_len,
+                        const float* scales, const float* means, const float* weights, int64_t n,
+                        int64_t stride_n, int64_t stride_k, int mode, int mem, int32_t max_bs_value,
+                        int32_t* symbols_out) {
+    flashgmm_stream s{};
+    s.scales = scales; s.means = means; s.weights = weights;
+    s.n = n; s.stride_n = stride_n; s.stride_k = stride_k;
+    s.max_bs_value = max_bs_value;
+    s.bytes = const_cast<uint8_t*>(encoded); s.bytes_cap = encoded_len;
+    s.symbols_out = symbols_out;
+    return run_batch(ctx, &s, 1, mode, mem, decode_stream);
+}
+
+int flashgmm_gmm_encode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem) {
+    return run_batch(ctx, streams, n_streams, mode, mem, encode_stream);
+}
+
+int flashgmm_gmm_decode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem) {
+    return run_batch(ctx, streams, n_streams, mode, mem, decode_stream);
+}
+
+// ---- host-only halves ----
+static int emit(BackBuffer& bb, uint8_t* out, size_t cap, size_t* out_len) {
+    *out_len = bb.bytes();
+    if (*out_len > cap) return fail(FLASHGMM_ENOSPC, "output buffer too small: need %zu bytes, have %zu", *out_len, cap);
+    memcpy(out, bb.data(), *out_len);
+    return FLASHGMM_OK;
+}
+
+int flashgmm_rans_push_packed(const uint32_t* packed, const int32_t* symbols, int64_t n, uint8_t* out,
+                              size_t out_cap, size_t* out_len) {
+    if (!out_len || (n > 0 && !packed) || n < 0 || (!out && out_cap)) return fail(FLASHGMM_EINVAL, "bad argument");
+    if (!symbols)
+        for (int64_t i = 0; i < n; ++i)
+            if ((packed[i] >> 16) == 0) return fail(FLASHGMM_EINVAL, "bypass record at %lld needs symbols", (long long)i);
+    BackBuffer bb((size_t)(n * 9 / 16) + 64);
+    RansEncoder64 enc;
+    enc.init(&bb);
+    enc.push_chunk_reverse(packed, symbols, n);
+    enc.flush();
+    return emit(bb, out, out_cap, out_len);
+}
+
+int flashgmm_rans_pop_table(const uint8_t* encoded, size_t encoded_len, const uint16_t* table,
+                            int64_t row_stride, int64_t n, int32_t R, int32_t* symbols_out) {
+    if (!encoded || n < 0 || (n > 0 && (!table || !symbols_out)) || R < 0 || row_stride < 2 * (int64_t)R + 3)
+        return fail(FLASHGMM_EINVAL, "bad argument");
+    RansDecoder64 dec;
+    dec.init(encoded, encoded_len);
+    const uint16_t* row = table;
+    for (int64_t i = 0; i < n; ++i, row += row_stride) {
+        const uint32_t cum = dec.get();
+        int32_t v;
+        if (cum == kMaxCdf) { dec.advance(kMaxCdf, 1); v = (int32_t)dec.bypass_raw(); }
+        else { uint32_t st, fr; v = search_row(row, R, cum, &st, &fr); dec.advance(st, fr); }
+        symbols_out[i] = v;
+    }
+    if (dec.overrun) return fail(FLASHGMM_ETRUNC, "bitstream truncated");
+    return FLASHGMM_OK;
+}
+
+static int check_table_args(const int32_t* indexes, int64_t n, const int32_t* cdfs, int64_t n_cdfs,
+                            int64_t cdf_stride, const int32_t* sizes, const int32_t* offsets) {
+    if (n < 0 || n_cdfs < 0 || (n > 0 && (!indexes || !cdfs || !sizes || !offsets)))
+        return fail(FLASHGMM_EINVAL, "bad argument");
+    for (int64_t c = 0; c < n_cdfs; ++c)
+        if (sizes[c] < 2 || sizes[c] > cdf_stride) return fail(FLASHGMM_EINVAL, "cdf_sizes[%lld]=%d invalid", (long long)c, sizes[c]);
+    for (int64_t i = 0; i < n; ++i)
+        if (indexes[i] < 0 || indexes[i] >= n_cdfs) return fail(FLASHGMM_EINVAL, "indexes[%lld]=%d out of range", (long long)i, indexes[i]);
+    return FLASHGMM_OK;
+}
+
+int flashgmm_rans_encode_table(const int32_t* symbols, const int32_t* indexes, int64_t n,
+                               const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
+                               const int32_t* cdf_sizes, const int32_t* offsets, uint8_t* out,
+                               size_t out_cap, size_t* out_len) {
+    if (!out_len || (n > 0 && !symbols)) return fail(FLASHGMM_EINVAL, "bad argument");
+    int rc = check_table_args(indexes, n, cdfs, n_cdfs, cdf_stride, cdf_sizes, offsets);
+    if (rc) return rc;
+    BackBuffer bb((size_t)(n * 9 / 16) + 64);
+    RansEncoder64 enc;
+    enc.init(&bb);
+    for (int64_t i = n - 1; i >= 0; --i) {             // reverse walk of rans_interface.cpp:343-398
+        bb.reserve(24);
+        const int32_t ci = indexes[i];
+        const int32_t* cdf = cdfs + (int64_t)ci * cdf_stride;
+        const int32_t max_value = cdf_sizes[ci] - 2;
+        int32_t value = symbols[i] - offsets[ci];
+        uint32_t raw = 0;
+        if (value < 0) { raw = (uint32_t)(-2 * value - 1); value = max_value; }
+        else if (value >= max_value) { raw = (uint32_t)(2 * (value - max_value)); value = max_value; }
+        if (value == max_value) {
+            int nb = 0;
+            while (nb < 8 && (raw >> (nb * 4)) != 0) ++nb;
+            for (int j = nb - 1; j >= 0; --j) enc.put_bits4((raw >> (4 * j)) & kBypassMax);
+            enc.put_bits4((uint32_t)nb);
+        }
+        const uint32_t start = (uint32_t)cdf[value] & 0xffffu;
+        const uint32_t freq = (uint32_t)(cdf[value + 1] - cdf[value]) & 0xffffu;
+        if (freq == 0) return fail(FLASHGMM_EINVAL, "zero-frequency symbol at %lld (invalid CDF)", (long long)i);
+        enc.put(start, freq);
+    }
+    enc.flush();
+    return emit(bb, out, out_cap, out_len);
+}
+
+int flashgmm_rans_decode_table(const uint8_t* encoded, size_t encoded_len, const int32_t* indexes,
+                               int64_t n, const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
+                               const int32_t* cdf_sizes, const int32_t* offsets, int32_t* symbols_out) {
+    if (!encoded || (n > 0 && !symbols_out)) return fail(FLASHGMM_EINVAL, "bad argument");
+    int rc = check_table_args(indexes, n, cdfs, n_cdfs, cdf_stride, cdf_sizes, offsets);
+    if (rc) return rc;
+    RansDecoder64 dec;
+    dec.init(encoded, encoded_len);
+    for (int64_t i = 0; i < n; ++i) {
+        const int32_t ci = indexes[i];
+        const int32_t* cdf = cdfs + (int64_t)ci * cdf_stride;
+        const int32_t sz = cdf_sizes[ci], max_value = sz - 2;
+        const uint32_t cum = dec.get();
+        const int32_t* it = std::lower_bound(cdf, cdf + sz, (int32_t)(cum + 1));
+        int32_t sidx = (int32_t)(it - cdf) - 1;
+        if (sidx < 0) sidx = 0;
+        if (sidx > max_value) sidx = max_value;
+        dec.advance((uint32_t)cdf[sidx], (uint32_t)(cdf[sidx + 1] - cdf[sidx]));
+        int32_t value = sidx;
+        if (value == max_value) {
+            int32_t vb = (int32_t)dec.get_bits4(), nb = vb;
+            while (vb == (int32_t)kBypassMax && !dec.overrun) { vb = (int32_t)dec.get_bits4(); nb += vb; }
+            int32_t raw = 0;
+            for (int32_t j = 0; j < nb && !dec.overrun; ++j) raw |= (int32_t)(dec.get_bits4() << ((j * 4) & 31));
+            value = raw >> 1;
+            if (raw & 1) value = -value - 1; else value += max_value;
+        }
+        symbols_out[i] = value + offsets[ci];
+    }
+    if (dec.overrun) return fail(FLASHGMM_ETRUNC, "bitstream truncated");
+    return FLASHGMM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,32 @@
+// gmm_kernels.h -- internal launcher interface between the C-ABI layer and the kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace flashgmm {
+
+// (N, 4) parameter views in element strides. The reference's callers hand over
+// K-major planes: stride_n == 1, stride_k == N (entropy_models.py:813-827).
+struct GmmParamsView {
+    const float* scales;
+    const float* means;
+    const float* weights;
+    int64_t stride_n;
+    int64_t stride_k;
+};
+
+// 0 = K-major 128-bit path, 1 = AoS (N,4) contiguous, 2 = generic strided.
+int gmm_layout_of(const GmmParamsView& p, const void* sym, const void* out);
+
+// bypass_flag (nullable, device, pre-zeroed): set to 1 if any symbol needs bypass.
+cudaError_t launch_gmm_startfreq(const int32_t* sym, const GmmParamsView& p, int64_t n, int mode,
+                                 uint32_t* out, uint32_t* bypass_flag, cudaStream_t st);
+
+// Row stride (uint16 elements) of the decode table for search radius R:
+// 2R+2 CDF entries + 1 flag slot, rounded up to a multiple of 8 (16-byte rows).
+int gmm_table_row_stride(int R);
+
+cudaError_t launch_gmm_cdf_table(const GmmParamsView& p, int64_t n, int mode, int R, uint16_t* table,
+                                 int row_stride, cudaStream_t st);
+
+}  // namespace flashgmm

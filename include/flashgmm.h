@@ -1,0 +1,164 @@
+/*
+ * flashgmm.h -- C ABI of libflashgmm_b200.so (sm_100a), the drop-in boundary for
+ * FlashGMM's Gaussian-mixture entropy-coding hot path.
+ *
+ * Each entry point cites the reference interface it replaces (paths relative to the
+ * reference repository root, tokkiwa/FlashGMM):
+ *   RI  = compressai/cpp_exts/rans/rans_interface.cpp
+ *   EM  = compressai/entropy_models/entropy_models.py
+ *
+ * Conventions
+ *  - plain pointers and sizes only; no ownership crosses the ABI (caller allocates).
+ *  - every function returns a flashgmm_status; flashgmm_last_error() gives the
+ *    message for the calling thread.
+ *  - GMM parameters are three float32 (N, 4) views given as base pointer + element
+ *    strides (stride_n, stride_k). The reference's callers pass K-major planes,
+ *    stride_n = 1, stride_k = N (EM:813-827); (N,4) row-major is stride_n = 4,
+ *    stride_k = 1. Any strides are accepted for device memory; host memory must be
+ *    one of those two layouts.
+ *  - `mem` says where symbols / parameters / decoded output live:
+ *    FLASHGMM_MEM_HOST (copied in chunks inside the call, pinned or pageable) or
+ *    FLASHGMM_MEM_DEVICE (used in place on the ctx's device). Bitstreams are
+ *    always host memory: the serial rANS state recurrence runs on the host.
+ *  - `mode` is APPROX_MODE with the reference's CODE numbering (RI:98, 223-233):
+ *    0 Polya, 1 Abramowitz-Stegun, 2 logistic.
+ *  - K is fixed at 4, the only instantiation the reference binds (RI:60, 982).
+ *  - a ctx serialises its calls internally; use one ctx per host thread for
+ *    concurrency. There is no CPU fallback: without a CUDA device ctx_create fails.
+ */
+#ifndef FLASHGMM_H_
+#define FLASHGMM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct flashgmm_ctx flashgmm_ctx;
+
+typedef enum {
+    FLASHGMM_OK = 0,
+    FLASHGMM_EINVAL = 1,   /* bad argument (null pointer, unsupported strides, mode, K) */
+    FLASHGMM_ECUDA = 2,    /* CUDA runtime error; message in flashgmm_last_error() */
+    FLASHGMM_ETRUNC = 3,   /* bitstream shorter than the reads it implies */
+    FLASHGMM_ENOSPC = 4    /* caller's output buffer too small; *out_len = needed */
+} flashgmm_status;
+
+enum { FLASHGMM_MEM_HOST = 0, FLASHGMM_MEM_DEVICE = 1 };
+
+int flashgmm_version(void);
+const char* flashgmm_last_error(void);
+
+/* Context = device + streams + staging buffers + host worker threads. */
+int flashgmm_ctx_create(int device, flashgmm_ctx** out);
+void flashgmm_ctx_destroy(flashgmm_ctx* ctx);
+
+/* Upper bound of an encoded stream for n symbols (every symbol bypassed):
+ * cf. the reference's n_entries + 16 words buffer, RI:563. */
+size_t flashgmm_max_encoded_bytes(int64_t n);
+
+/* ---- kernel-level entry points (device pointers, asynchronous on `stream`) ---- */
+
+/* Per-symbol rANS (start, freq): out[i] = start | freq << 16; freq == 0 marks a
+ * symbol the reference sends through bypass (pmf == 0).  Replaces the loop body of
+ * BufferedRansEncoder::encode_with_indexes_gmm<4>, RI:486-522 (+ _fast_gmm_cdf<4>
+ * RI:259-284 and the approximations RI:135-214). `stream` is a cudaStream_t (NULL =
+ * the ctx's own stream, synchronised before return). */
+int flashgmm_gmm_startfreq(flashgmm_ctx* ctx, const int32_t* symbols_d, const float* scales_d,
+                           const float* means_d, const float* weights_d, int64_t n,
+                           int64_t stride_n, int64_t stride_k, int mode, uint32_t* packed_out_d,
+                           void* stream);
+
+/* Row stride, in uint16 elements, of the decode table for search radius R. */
+int flashgmm_gmm_table_row_stride(int32_t R);
+
+/* Quantised CDF rows for the search decoder: table[i*row_stride + j] =
+ * uint16(cdf_i(v - 0.5) * 65535), v = j - R, j in [0, 2R+2); slot 2R+2 is 1 when the
+ * row is not non-decreasing. Replaces the CDF evaluations inside the binary search
+ * of RansDecoder::decode_with_indexes_gmm<4>, RI:833-862. */
+int flashgmm_gmm_cdf_table(flashgmm_ctx* ctx, const float* scales_d, const float* means_d,
+                           const float* weights_d, int64_t n, int64_t stride_n, int64_t stride_k,
+                           int mode, int32_t R, uint16_t* table_d, int64_t row_stride, void* stream);
+
+/* ---- whole-call entry points (what the reference's pybind methods do) ---- */
+
+/* RansEncoder.encode_with_indexes_gmm(symbols, scales, means, weights, max_value)
+ * -> bytes, RI:609-617 (+ RI:458-585). Byte-identical output. max_value is unused by
+ * the reference and therefore not a parameter. */
+int flashgmm_gmm_encode(flashgmm_ctx* ctx, const int32_t* symbols, const float* scales,
+                        const float* means, const float* weights, int64_t n, int64_t stride_n,
+                        int64_t stride_k, int mode, int mem, uint8_t* out, size_t out_cap,
+                        size_t* out_len);
+
+/* RansDecoder.decode_with_indexes_gmm(encoded, scales, means, weights, max_bs_value)
+ * -> int32[N], RI:766-883. symbols_out lives in `mem`. */
+int flashgmm_gmm_decode(flashgmm_ctx* ctx, const uint8_t* encoded, size_t encoded_len,
+                        const float* scales, const float* means, const float* weights, int64_t n,
+                        int64_t stride_n, int64_t stride_k, int mode, int mem, int32_t max_bs_value,
+                        int32_t* symbols_out);
+
+/* Many independent streams in one call (one per checkerboard pass / channel group /
+ * image): kernels are queued back to back and the serial host coding of the
+ * streams runs on the ctx's worker threads. */
+typedef struct {
+    const int32_t* symbols;   /* encode: in.  decode: unused (may be NULL) */
+    const float* scales;
+    const float* means;
+    const float* weights;
+    int64_t n;
+    int64_t stride_n;
+    int64_t stride_k;
+    int32_t max_bs_value;     /* decode only */
+    uint8_t* bytes;           /* encode: out buffer.  decode: in stream */
+    size_t bytes_cap;         /* encode: capacity.    decode: stream length */
+    size_t bytes_len;         /* encode: out, produced length */
+    int32_t* symbols_out;     /* decode: out */
+    int status;               /* out: per-stream flashgmm_status */
+} flashgmm_stream;
+
+int flashgmm_gmm_encode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode,
+                              int mem);
+int flashgmm_gmm_decode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode,
+                              int mem);
+
+/* ---- host-only halves (no GPU): the serial rANS recurrence ---- */
+
+/* Push packed (start|freq<<16, freq==0 = bypass -> needs symbols[i]) records:
+ * BufferedRansEncoder::flush, RI:557-585, incl. the bypass payload RI:524-552. */
+int flashgmm_rans_push_packed(const uint32_t* packed, const int32_t* symbols, int64_t n,
+                              uint8_t* out, size_t out_cap, size_t* out_len);
+
+/* Pop n symbols using precomputed rows (flashgmm_gmm_cdf_table layout):
+ * the state/search/advance loop of RI:793-883. */
+int flashgmm_rans_pop_table(const uint8_t* encoded, size_t encoded_len, const uint16_t* table,
+                            int64_t row_stride, int64_t n, int32_t R, int32_t* symbols_out);
+
+/* Table-driven coder kept for the hyper-latent z branch:
+ * RansEncoder.encode_with_indexes(symbols, indexes, cdfs, cdfs_sizes, offsets), RI:334-399, 587-598
+ * RansDecoder.decode_with_indexes(encoded, indexes, cdfs, cdfs_sizes, offsets), RI:619-688.
+ * cdfs is a dense [n_cdfs][cdf_stride] int32 matrix (CompressAI's _quantized_cdf). */
+int flashgmm_rans_encode_table(const int32_t* symbols, const int32_t* indexes, int64_t n,
+                               const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
+                               const int32_t* cdf_sizes, const int32_t* offsets, uint8_t* out,
+                               size_t out_cap, size_t* out_len);
+int flashgmm_rans_decode_table(const uint8_t* encoded, size_t encoded_len, const int32_t* indexes,
+                               int64_t n, const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
+                               const int32_t* cdf_sizes, const int32_t* offsets, int32_t* symbols_out);
+
+/* Kernel launches issued by this process through the library (bench.py's gpu_launches). */
+uint64_t flashgmm_launch_count(void);
+
+/* Optional live kernel timing for roofline reports: when enabled, every kernel the
+ * whole-call entry points launch is bracketed by CUDA events on its own stream.
+ * kind 0 = gmm_startfreq (algorithmic bytes 56/symbol), 1 = gmm_cdf_table
+ * (48 + 2*row_stride bytes/symbol). */
+void flashgmm_profile_enable(int on);
+void flashgmm_profile_reset(void);
+int flashgmm_profile_read(int kind, double* total_ms, uint64_t* launches, double* algorithmic_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLASHGMM_H_ */

@@ -1,0 +1,229 @@
+"""CPU-side checks of the product library: ABI completeness and the serial host
+halves (rANS push/pop, table coder) against the oracle. No GPU compute is called."""
+import ctypes as C
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from flashgmm_b200 import _lib, ans, synth
+from oracle import port
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = (ROOT / "include" / "flashgmm.h").read_text()
+    declared = set(re.findall(r"\b(flashgmm_[a-z0-9_]+)\s*\(", hdr))
+    declared -= {"flashgmm_ctx", "flashgmm_status", "flashgmm_stream"}
+    assert len(declared) >= 17
+    L = C.CDLL(str(_lib.LIB_PATH))
+    missing = [s for s in sorted(declared) if not hasattr(L, s)]
+    assert not missing, missing
+    assert set(_lib._SIGS) == declared          # the ctypes table binds exactly the header
+    assert _lib.lib().flashgmm_version() >= 100
+
+
+def test_stream_struct_layout_matches_header():
+    # 7 pointers/int64 + int32 (+pad) + ptr + 2 size_t + ptr + int (+pad)
+    assert C.sizeof(_lib.Stream) == 8 * 7 + 8 + 8 + 16 + 8 + 8
+
+
+def test_math_constants_are_the_reference_literals():
+    src = (ROOT / "flashgmm_b200/csrc/gmm_math.cuh").read_text()
+    want = {
+        "EXP_HI": np.float32(88.3762626647949), "EXP_LO": np.float32(-88.3762626647949),
+        "LOG2EF": np.float32(1.44269504088896341), "EXP_C1": np.float32(0.693359375),
+        "EXP_C2": np.float32(-2.12194440e-4), "EXP_P0": np.float32(1.9875691500E-4),
+        "EXP_P1": np.float32(1.3981999507E-3), "EXP_P2": np.float32(8.3334519073E-3),
+        "EXP_P3": np.float32(4.1665795894E-2), "EXP_P4": np.float32(1.6666665459E-1),
+        "EXP_P5": np.float32(5.0000001201E-1),
+        "M2_OVER_PI": np.float32(-2.0) / np.float32(3.14159265358979323846),
+        "INV_SQRT_2PI": np.float32(0.3989422804014327), "AS_P": np.float32(0.2316419),
+        "AS_B1": np.float32(0.319381530), "AS_B2": np.float32(-0.356563782),
+        "AS_B3": np.float32(1.781477937), "AS_B4": np.float32(-1.821255978),
+        "AS_B5": np.float32(1.330274429), "LOGI_K": np.float32(1.702),
+    }
+    for k, v in want.items():
+        m = re.search(r"#define FGMM_%s\s+FGMM_F\(0x([0-9a-f]{8})u\)" % k, src)
+        assert m, k
+        assert m.group(1) == "%08x" % np.float32(v).view(np.uint32), k
+
+
+def _packed_from_oracle(sym, sg, mu, w, mode):
+    st, fr, bp = port.gmm_startfreq(sym, sg, mu, w, mode)
+    p = st.astype(np.uint32) | (fr.astype(np.uint32) << 16)
+    p[bp == 1] = 0xFFFF
+    return p
+
+
+def _push(packed, sym):
+    L = _lib.lib()
+    cap = packed.size * 48 + 64
+    out = np.empty(cap, np.uint8)
+    n = C.c_size_t()
+    _lib.check(L.flashgmm_rans_push_packed(packed.ctypes.data, sym.ctypes.data if sym is not None else None,
+                                           packed.size, out.ctypes.data, cap, C.byref(n)))
+    return out[: n.value].tobytes()
+
+
+CASES = [dict(n=50_000, seed=31), dict(n=20_000, seed=32, sigma_span=0.0),
+         dict(n=20_000, seed=33, sigma_span=0.05, offcentre=9.0), dict(n=4099, seed=34), dict(n=1, seed=35),
+         dict(n=0, seed=36)]
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+@pytest.mark.parametrize("kw", CASES, ids=lambda k: f"n{k['n']}s{k['seed']}")
+def test_host_push_and_pop_match_oracle(kw, mode):
+    sym, sg, mu, w = synth.gmm_numpy(**kw)
+    sym = sym.copy()
+    if sym.size > 10:
+        sym[3], sym[4] = 2**31 - 1, -2**31          # 8-nibble bypass payloads
+    packed = _packed_from_oracle(sym, sg, mu, w, mode)
+    want = port.gmm_encode(sym, sg, mu, w, mode)
+    assert _push(packed, sym) == want               # reciprocal-multiply push == div/mod push
+    # pop on oracle-made rows (radius limited: rows are 2R+2 wide)
+    core = np.clip(sym, -60, 60)
+    R = synth.search_radius(core)
+    want = port.gmm_encode(core, sg, mu, w, mode)
+    L = _lib.lib()
+    rs = L.flashgmm_gmm_table_row_stride(R)
+    tab = port.gmm_cdf_table(sg, mu, w, R, mode)
+    T = np.zeros((core.size, rs), np.uint16)
+    T[:, : 2 * R + 2] = tab
+    T[:, 2 * R + 2] = (np.diff(tab.astype(np.int32), axis=1) < 0).any(1)
+    out = np.empty(core.size, np.int32)
+    buf = np.frombuffer(want, np.uint8)
+    _lib.check(L.flashgmm_rans_pop_table(buf.ctypes.data, buf.size, T.ctypes.data, rs, core.size, R, out.ctypes.data))
+    assert np.array_equal(out, port.gmm_decode(want, sg, mu, w, R, mode))
+    assert np.array_equal(out, core)
+
+
+def test_pop_replays_reference_search_on_non_monotone_rows():
+    """Rows that are not non-decreasing must give what the reference's binary search gives."""
+    r = np.random.default_rng(7)
+    n, R = 4000, 9
+    L = _lib.lib()
+    rs = L.flashgmm_gmm_table_row_stride(R)
+    W = 2 * R + 2
+    rows = np.sort(r.integers(0, 65535, (n, W)), axis=1).astype(np.uint16)
+    rows[:, 0] = 0
+    swap = r.integers(1, W - 1, n)
+    ar = np.arange(n)
+    a, b = rows[ar, swap].copy(), rows[ar, swap + 1].copy()
+    rows[ar, swap], rows[ar, swap + 1] = b, a                      # one inversion per row
+    T = np.zeros((n, rs), np.uint16)
+    T[:, :W] = rows
+    T[:, W] = (np.diff(rows.astype(np.int32), axis=1) < 0).any(1)
+    # a stream of arbitrary states: random words are a valid (if meaningless) rANS stream
+    words = r.integers(0, 2**32, 3 * n + 8, dtype=np.uint64).astype(np.uint32)
+    words[1] |= 0x80000000 >> 0
+    enc = words.tobytes()
+    out = np.empty(n, np.int32)
+    rc = L.flashgmm_rans_pop_table(enc, len(enc), T.ctypes.data, rs, n, R, out.ctypes.data)
+    assert rc == 0
+    # python replay of rans_interface.cpp:793-883 on the same rows
+    p = 2
+    x = int(words[0]) | (int(words[1]) << 32)
+    exp = np.empty(n, np.int32)
+    for i in range(n):
+        cum = x & 0xFFFF
+        if cum == 65535:
+            pytest.skip("random stream hit the bypass marker")
+        s_, e_, mid = -R, R, 0
+        while s_ <= e_:
+            mid = s_ + (e_ - s_) // 2 if (e_ - s_) >= 0 else s_
+            c1, c2 = int(rows[i, mid + R]), int(rows[i, mid + R + 1])
+            if c1 <= cum < c2:
+                break
+            elif c1 > cum:
+                e_ = mid - 1
+            else:
+                s_ = mid + 1
+        c1, c2 = int(rows[i, mid + R]), int(rows[i, mid + R + 1])
+        pmf = (c2 - c1) & 0xFFFF or 1
+        x = pmf * (x >> 16) + (x & 0xFFFF) - c1
+        x &= (1 << 64) - 1
+        if x < (1 << 31):
+            x = (x << 32) | int(words[p]); p += 1
+        exp[i] = mid
+    assert np.array_equal(out, exp)
+
+
+def test_reciprocal_push_equals_division_for_extreme_states():
+    """Drive the encoder state across its whole range with every interesting freq."""
+    r = np.random.default_rng(3)
+    freqs = np.concatenate([np.arange(1, 300), [4095, 4096, 4097, 32767, 32768, 32769, 65534, 65535],
+                            r.integers(1, 65536, 3000)]).astype(np.uint32)
+    for rep in range(3):
+        f = r.permutation(np.tile(freqs, 4))
+        start = (r.integers(0, 65536, f.size) % (65536 - f + 1)).astype(np.uint32)
+        packed = start | (f << 16)
+        # python big-int reference of rans64.h:77-103
+        x = 1 << 31
+        words = []
+        for s_, f_ in zip(start[::-1].tolist(), f[::-1].tolist()):
+            if x >= ((1 << 47) * f_):
+                words.append(x & 0xFFFFFFFF); x >>= 32
+            x = ((x // f_) << 16) + (x % f_) + s_
+        words += [x >> 32, x & 0xFFFFFFFF]
+        want = np.array(words[::-1], np.uint32).tobytes()
+        assert _push(packed, None) == want
+
+
+def test_table_coder_matches_oracle():
+    r = np.random.default_rng(5)
+    n_cdfs, width = 5, 64
+    cdfs = np.zeros((n_cdfs, width), np.int32)
+    sizes = np.zeros(n_cdfs, np.int32)
+    for c in range(n_cdfs):
+        m = int(r.integers(3, width - 2))
+        q = np.maximum(1, np.floor(r.dirichlet(np.ones(m + 1)) * 65000)).astype(np.int64)
+        q[np.argmax(q)] += 65536 - q.sum()
+        cdfs[c, 1:m + 2] = np.cumsum(q)
+        sizes[c] = m + 2
+    offsets = -(sizes // 2).astype(np.int32)
+    n = 20000
+    idx = r.integers(0, n_cdfs, n).astype(np.int32)
+    sym = r.normal(0, 8, n).round().astype(np.int32)
+    sym[:6] = [2**26, -2**26, 0, 1, -1, 77]
+    want = port.table_encode(sym, idx, cdfs, sizes, offsets)
+    got = ans.table_encode(sym, idx, [row[:s].tolist() for row, s in zip(cdfs, sizes)], sizes.tolist(), offsets.tolist())
+    assert got == want
+    assert np.array_equal(ans.table_decode(want, idx, cdfs, sizes, offsets), sym)
+    assert ans.RansDecoder().decode_with_indexes(want, idx.tolist(), cdfs.tolist(), sizes.tolist(), offsets.tolist()) == sym.tolist()
+    assert ans.table_encode([], [], cdfs, sizes, offsets) == port.table_encode(sym[:0], idx[:0], cdfs, sizes, offsets)
+
+
+def test_error_behaviour():
+    L = _lib.lib()
+    out = np.empty(8, np.uint8)
+    n = C.c_size_t()
+    pk = np.array([0xFFFF], np.uint32)           # bypass record without symbols
+    assert L.flashgmm_rans_push_packed(pk.ctypes.data, None, 1, out.ctypes.data, 8, C.byref(n)) == _lib.EINVAL
+    assert b"needs symbols" in L.flashgmm_last_error()
+    pk = np.array([1 | (5 << 16)] * 100, np.uint32)
+    assert L.flashgmm_rans_push_packed(pk.ctypes.data, None, 100, out.ctypes.data, 8, C.byref(n)) == _lib.ENOSPC
+    assert n.value > 8
+    # truncated stream
+    R = 3
+    rs = L.flashgmm_gmm_table_row_stride(R)
+    T = np.zeros((50, rs), np.uint16)
+    T[:, : 2 * R + 2] = np.linspace(0, 65535, 2 * R + 2).astype(np.uint16)
+    o = np.empty(50, np.int32)
+    enc = np.array([0x12345678, 0x80000000 >> 1], np.uint32).tobytes()   # state only, no renorm words
+    assert L.flashgmm_rans_pop_table(enc, len(enc), T.ctypes.data, rs, 50, R, o.ctypes.data) == _lib.ETRUNC
+    with pytest.raises(ValueError):
+        ans.set_approx_mode(3)
+    assert L.flashgmm_max_encoded_bytes(10) == 4 * (100 + 16)
+
+
+def test_approx_mode_env_parsing(monkeypatch):
+    for val, want in [("1", 1), ("2", 2), ("7", 0), ("x", 0), ("-1", 0)]:
+        monkeypatch.setenv("APPROX_MODE", val)
+        ans._mode = None
+        assert ans.get_approx_mode() == want
+    monkeypatch.delenv("APPROX_MODE")
+    ans._mode = None
+    assert ans.get_approx_mode() == 0
