@@ -405,19 +405,7 @@ int decode_stream(flashgmm_ctx* ctx, Lane& L, flashgmm_stream& s, int mode, int 
         prof_collect(S);
         const uint16_t* row = static_cast<const uint16_t*>(S.h_out.p);
         int32_t* o = out_h + c0;
-        for (int64_t i = 0; i < cnt; ++i, row += rs) {
-            const uint32_t cum = dec.get();
-            int32_t v;
-            if (__builtin_expect(cum == kMaxCdf, 0)) {
-                dec.advance(kMaxCdf, 1);
-                v = (int32_t)dec.bypass_raw();
-            } else {
-                uint32_t st, fr;
-                v = search_row(row, R, cum, &st, &fr);
-                dec.advance(st, fr);
-            }
-            o[i] = v;
-        }
+        pop_rows(dec, row, rs, R, cnt, o);
         if (mem == FLASHGMM_MEM_DEVICE)
             CU_TRY(cudaMemcpyAsync(s.symbols_out + c0, o, (size_t)cnt * 4, cudaMemcpyHostToDevice, S.st));
         if (q + kSlots < nch && (rc = issue(q + kSlots))) return rc;
@@ -639,18 +627,11 @@ int flashgmm_rans_push_packed(const uint32_t* packed, const int32_t* symbols, in
 
 int flashgmm_rans_pop_table(const uint8_t* encoded, size_t encoded_len, const uint16_t* table,
                             int64_t row_stride, int64_t n, int32_t R, int32_t* symbols_out) {
-    if (!encoded || n < 0 || (n > 0 && (!table || !symbols_out)) || R < 0 || row_stride < 2 * (int64_t)R + 3)
+    if (!encoded || n < 0 || (n > 0 && (!table || !symbols_out)) || R < 0 || row_stride != gmm_table_row_stride(R))
         return fail(FLASHGMM_EINVAL, "bad argument");
     RansDecoder64 dec;
     dec.init(encoded, encoded_len);
-    const uint16_t* row = table;
-    for (int64_t i = 0; i < n; ++i, row += row_stride) {
-        const uint32_t cum = dec.get();
-        int32_t v;
-        if (cum == kMaxCdf) { dec.advance(kMaxCdf, 1); v = (int32_t)dec.bypass_raw(); }
-        else { uint32_t st, fr; v = search_row(row, R, cum, &st, &fr); dec.advance(st, fr); }
-        symbols_out[i] = v;
-    }
+    pop_rows(dec, table, row_stride, R, n, symbols_out);
     if (dec.overrun) return fail(FLASHGMM_ETRUNC, "bitstream truncated");
     return FLASHGMM_OK;
 }

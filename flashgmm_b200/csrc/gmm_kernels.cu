@@ -113,27 +113,39 @@ gmm_startfreq_scalar_kernel(const int32_t* __restrict__ sym, GmmParamsView p, in
 }
 
 // ---- decode side: quantised CDF rows ----
+// Row layout (uint16 elements), R = search radius, W = 2R+2:
+//   [0, W)            T[j] = q16(cdf(j - R - 0.5))
+//   [W]               1 if T is not non-decreasing (host then replays the reference's search)
+//   (W, lut_off)      zero padding, lut_off = round_up(W+1, 8)
+//   [lut_off, +32)    jump table: lut[b] = max{ j in [0,2R] : T[j] <= b*2048 } (0 if none), so the
+//                     host starts its scan for cum at lut[cum >> 11] instead of at -R.
 constexpr int kTabThreads = 128;   // symbols per block
 constexpr int kTabTile = 64;       // uint16 entries per tile (32 words)
 constexpr int kTabTileWords = kTabTile / 2;
+constexpr int kLutBuckets = 32;
+constexpr int kLutShift = 11;
 
 template <int MODE>
 __global__ void __launch_bounds__(kTabThreads)
 gmm_cdf_table_kernel(GmmParamsView p, int64_t n, int R, uint16_t* __restrict__ table, int row_stride) {
     __shared__ uint32_t tile[kTabThreads][kTabTileWords + 1];
+    __shared__ uint32_t lut_s[kTabThreads][kLutBuckets / 2 + 1];
     const int64_t row0 = (int64_t)blockIdx.x * kTabThreads;
     const int64_t i = row0 + threadIdx.x;
     const bool live = i < n;
     float mu[4] = {0, 0, 0, 0}, sg[4] = {1, 1, 1, 1}, w[4] = {0, 0, 0, 0};
     if (live) load_generic(p, i, mu, sg, w);
 
-    const int W = 2 * R + 2;               // real entries; slot W holds the non-monotone flag
+    const int W = 2 * R + 2;
+    const int lut_off = (W + 1 + 7) & ~7;
     uint32_t prev = 0, nonmono = 0;
+    int cn = 0;                                   // next jump-table bucket to fill
+    uint16_t* my_lut = reinterpret_cast<uint16_t*>(lut_s[threadIdx.x]);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint32_t* tab32 = reinterpret_cast<uint32_t*>(table);
     const int row_words = row_stride >> 1;
 
-    for (int j0 = 0; j0 < row_stride; j0 += kTabTile) {
+    for (int j0 = 0; j0 < lut_off; j0 += kTabTile) {
         if (live) {
 #pragma unroll 2
             for (int jj = 0; jj < kTabTile; jj += 2) {
@@ -147,6 +159,11 @@ gmm_cdf_table_kernel(GmmParamsView p, int64_t n, int R, uint16_t* __restrict__ t
                         c = gmm_q16<MODE>(__fsub_rn((float)(j - R), 0.5f), mu, sg, w);
                         nonmono |= (c < prev);
                         prev = c;
+                        if (j < W - 1) {          // candidates are j in [0, 2R]
+                            while (cn < kLutBuckets && (uint32_t)(cn << kLutShift) < c) {
+                                my_lut[cn++] = (uint16_t)(j > 0 ? j - 1 : 0);
+                            }
+                        }
                     } else if (j == W) {
                         c = nonmono;
                     }
@@ -160,10 +177,17 @@ gmm_cdf_table_kernel(GmmParamsView p, int64_t n, int R, uint16_t* __restrict__ t
         const int wbase = j0 >> 1;
         for (int r = warp; r < kTabThreads; r += kTabThreads / 32) {
             int64_t row = row0 + r;
-            if (row < n && wbase + lane < row_words)
+            if (row < n && wbase + lane < (lut_off >> 1))
                 tab32[row * row_words + wbase + lane] = tile[r][lane];
         }
         __syncthreads();
+    }
+    if (live) while (cn < kLutBuckets) my_lut[cn++] = (uint16_t)(2 * R);
+    __syncthreads();
+    // jump tables: 16 words per row, two rows per warp pass
+    for (int r = warp * 2 + (lane >> 4); r < kTabThreads; r += (kTabThreads / 32) * 2) {
+        int64_t row = row0 + r;
+        if (row < n) tab32[row * row_words + (lut_off >> 1) + (lane & 15)] = lut_s[r][lane & 15];
     }
 }
 
@@ -211,7 +235,8 @@ cudaError_t launch_gmm_startfreq(const int32_t* sym, const GmmParamsView& p, int
     }
 }
 
-int gmm_table_row_stride(int R) { return ((2 * R + 3) + 7) & ~7; }
+int gmm_table_lut_offset(int R) { return ((2 * R + 3) + 7) & ~7; }
+int gmm_table_row_stride(int R) { return gmm_table_lut_offset(R) + kLutBuckets; }
 
 cudaError_t launch_gmm_cdf_table(const GmmParamsView& p, int64_t n, int mode, int R, uint16_t* table,
                                  int row_stride, cudaStream_t st) {

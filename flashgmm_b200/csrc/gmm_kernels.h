@@ -22,8 +22,9 @@ int gmm_layout_of(const GmmParamsView& p, const void* sym, const void* out);
 cudaError_t launch_gmm_startfreq(const int32_t* sym, const GmmParamsView& p, int64_t n, int mode,
                                  uint32_t* out, uint32_t* bypass_flag, cudaStream_t st);
 
-// Row stride (uint16 elements) of the decode table for search radius R:
-// 2R+2 CDF entries + 1 flag slot, rounded up to a multiple of 8 (16-byte rows).
+// Decode-table row for search radius R (uint16 elements): 2R+2 CDF entries, 1 flag
+// slot, zero padding up to lut_offset (multiple of 8), then a 32-entry jump table.
+int gmm_table_lut_offset(int R);
 int gmm_table_row_stride(int R);
 
 cudaError_t launch_gmm_cdf_table(const GmmParamsView& p, int64_t n, int mode, int R, uint16_t* table,

@@ -17,6 +17,9 @@
 #include <string.h>
 #include <stdlib.h>
 #include <mutex>
+#if defined(__AVX2__)
+#include <immintrin.h>
+#endif
 #include <vector>
 
 namespace flashgmm {
@@ -180,17 +183,61 @@ struct RansDecoder64 {
 };
 
 // Replays RansDecoder::decode_with_indexes_gmm<4> (rans_interface.cpp:766-883) on
-// the GPU-computed rows. row[j] = q16(cdf(v - 0.5)), v = j - R, j in [0, 2R+2);
-// row[2R+2] != 0 flags a row that is not non-decreasing (then the reference's
-// binary search is replayed probe by probe; otherwise a branch-free count gives
-// the same `mid`, including the fall-off-the-end cases).
-inline int32_t search_row(const uint16_t* row, int32_t R, uint32_t cum, uint32_t* start, uint32_t* freq) {
-    const int32_t W1 = 2 * R + 1;        // candidates v = -R..R -> j = 0..2R
+// the GPU-computed rows (layout: gmm_kernels.cu). row[j] = q16(cdf(v - 0.5)),
+// v = j - R, j in [0, 2R+2); row[2R+2] != 0 flags a row that is not non-decreasing:
+// then the reference's binary search is replayed probe by probe. Otherwise the
+// search result is max{ j in [0,2R] : row[j] <= cum } (0 if none) -- the same `mid`
+// the reference reaches, including its fall-off-the-end cases -- found by a short
+// forward scan from the row's jump table entry for cum's bucket.
+constexpr int kLutShift = 11;
+constexpr int kLutBuckets = 32;
+inline int table_lut_offset(int32_t R) { return ((2 * R + 3) + 7) & ~7; }
+
+// Per-call search plan: short rows are counted whole with AVX2 (no dependent jump-table
+// load, no data-dependent branch); long rows start from the jump table.
+struct SearchPlan {
+    int32_t R = 0;
+    int lut_off = 0;
+    int nvec = 0;                 // 16-lane vectors covering the candidates j in [0, 2R]; 0 = use the jump table
+    uint32_t lane_mask[4] = {0, 0, 0, 0};   // movemask bits (2 per lane) of valid candidates per vector
+    explicit SearchPlan(int32_t r) : R(r), lut_off(table_lut_offset(r)) {
+        const int cand = 2 * r + 1;
+#if defined(__AVX2__)
+        if (cand <= 64) {
+            nvec = (cand + 15) / 16;
+            for (int v = 0; v < nvec; ++v) {
+                int lanes = cand - 16 * v;
+                if (lanes > 16) lanes = 16;
+                lane_mask[v] = lanes == 16 ? 0xffffffffu : ((1u << (2 * lanes)) - 1u);
+            }
+        }
+#endif
+    }
+};
+
+inline int32_t search_row(const uint16_t* row, const SearchPlan& P, uint32_t cum, uint32_t* start,
+                          uint32_t* freq) {
+    const int32_t R = P.R;
     int32_t j;
     if (__builtin_expect(row[2 * R + 2] == 0, 1)) {
-        int32_t cnt = 0;
-        for (int32_t k = 0; k < W1; ++k) cnt += (row[k] <= cum);
-        j = cnt > 0 ? cnt - 1 : 0;
+#if defined(__AVX2__)
+        if (P.nvec) {
+            const __m256i c = _mm256_set1_epi16((short)cum);
+            uint32_t bits = 0;
+            for (int v = 0; v < P.nvec; ++v) {
+                __m256i t = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(row + 16 * v));
+                __m256i le = _mm256_cmpeq_epi16(_mm256_min_epu16(t, c), t);      // t <= cum (unsigned)
+                bits += (uint32_t)__builtin_popcount((uint32_t)_mm256_movemask_epi8(le) & P.lane_mask[v]);
+            }
+            const int32_t cnt = (int32_t)(bits >> 1);
+            j = cnt > 0 ? cnt - 1 : 0;
+        } else
+#endif
+        {
+            j = row[P.lut_off + (cum >> kLutShift)];
+            const int32_t jmax = 2 * R;
+            while (j < jmax && row[j + 1] <= cum) ++j;
+        }
     } else {
         int32_t s = -R, e = R, mid = 0;
         while (s <= e) {
@@ -207,6 +254,26 @@ inline int32_t search_row(const uint16_t* row, int32_t R, uint32_t cum, uint32_t
     if (pmf == 0) pmf = 1;               // rans_interface.cpp:866-875 (the start clamp there can never trigger)
     *start = c1; *freq = pmf;
     return j - R;
+}
+
+// Pop `cnt` symbols whose rows start at `row` (the loop of rans_interface.cpp:798-881).
+inline void pop_rows(RansDecoder64& dec, const uint16_t* row, int64_t rs, int32_t R, int64_t cnt, int32_t* out) {
+    const SearchPlan plan(R);
+    for (int64_t i = 0; i < cnt; ++i, row += rs) {
+        __builtin_prefetch(row + 8 * rs);
+        __builtin_prefetch(row + 8 * rs + 32);
+        const uint32_t cum = dec.get();
+        int32_t v;
+        if (__builtin_expect(cum == kMaxCdf, 0)) {
+            dec.advance(kMaxCdf, 1);
+            v = (int32_t)dec.bypass_raw();
+        } else {
+            uint32_t st, fr;
+            v = search_row(row, plan, cum, &st, &fr);
+            dec.advance(st, fr);
+        }
+        out[i] = v;
+    }
 }
 
 }  // namespace flashgmm

@@ -13,6 +13,7 @@ import torch
 
 from flashgmm_b200 import _lib, ans, synth
 from oracle import port, ref
+from helpers import lut_offset, make_rows
 
 pytestmark = pytest.mark.gpu
 GOLD = Path(__file__).resolve().parent / "golden"
@@ -73,7 +74,7 @@ def test_startfreq_extreme_arguments(mode):
     sym = np.clip(sym, -2**31, 2**31 - 1).astype(np.int32)
     mu[:, 1000:1100] = sym[1000:1100] - 0.5          # t == 0 exactly at x1
     mu[:, 1100:1200] = sym[1100:1200] + 0.5
-    sg, mu, w = sg.T, mu.T, w.T
+    sg, mu, w = (np.ascontiguousarray(x).T for x in (sg, mu, w))
     got = startfreq_gpu(sym, sg, mu, w, mode)
     want = oracle_packed(sym, sg, mu, w, mode)
     assert np.array_equal(got, want)
@@ -115,9 +116,11 @@ def test_cdf_table_kernel_bit_exact(R, mode):
     got = tab.cpu().numpy().view(np.uint16)
     want = port.gmm_cdf_table(sg, mu, w, R, mode)
     assert np.array_equal(got[:, : 2 * R + 2], want)
-    nonmono = (np.diff(want.astype(np.int32), axis=1) < 0).any(1)
+    rows = make_rows(want, R)
+    nonmono = rows[:, 2 * R + 2] != 0
     assert np.array_equal(got[:, 2 * R + 2] != 0, nonmono)
-    assert (got[:, 2 * R + 3:] == 0).all()
+    assert (got[:, 2 * R + 3: lut_offset(R)] == 0).all()
+    assert np.array_equal(got[~nonmono, lut_offset(R):], rows[~nonmono, lut_offset(R):])   # jump tables
 
 
 @pytest.mark.parametrize("key", sorted(MD5))

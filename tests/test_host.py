@@ -9,6 +9,7 @@ import pytest
 
 from flashgmm_b200 import _lib, ans, synth
 from oracle import port
+from helpers import make_rows, row_stride
 
 ROOT = Path(__file__).resolve().parents[1]
 
@@ -89,10 +90,8 @@ def test_host_push_and_pop_match_oracle(kw, mode):
     want = port.gmm_encode(core, sg, mu, w, mode)
     L = _lib.lib()
     rs = L.flashgmm_gmm_table_row_stride(R)
-    tab = port.gmm_cdf_table(sg, mu, w, R, mode)
-    T = np.zeros((core.size, rs), np.uint16)
-    T[:, : 2 * R + 2] = tab
-    T[:, 2 * R + 2] = (np.diff(tab.astype(np.int32), axis=1) < 0).any(1)
+    assert rs == row_stride(R)
+    T = make_rows(port.gmm_cdf_table(sg, mu, w, R, mode), R)
     out = np.empty(core.size, np.int32)
     buf = np.frombuffer(want, np.uint8)
     _lib.check(L.flashgmm_rans_pop_table(buf.ctypes.data, buf.size, T.ctypes.data, rs, core.size, R, out.ctypes.data))
@@ -113,9 +112,8 @@ def test_pop_replays_reference_search_on_non_monotone_rows():
     ar = np.arange(n)
     a, b = rows[ar, swap].copy(), rows[ar, swap + 1].copy()
     rows[ar, swap], rows[ar, swap + 1] = b, a                      # one inversion per row
-    T = np.zeros((n, rs), np.uint16)
-    T[:, :W] = rows
-    T[:, W] = (np.diff(rows.astype(np.int32), axis=1) < 0).any(1)
+    T = make_rows(rows, R)
+    assert T[:, W].all()
     # a stream of arbitrary states: random words are a valid (if meaningless) rANS stream
     words = r.integers(0, 2**32, 3 * n + 8, dtype=np.uint64).astype(np.uint32)
     words[1] |= 0x80000000 >> 0
@@ -209,8 +207,7 @@ def test_error_behaviour():
     # truncated stream
     R = 3
     rs = L.flashgmm_gmm_table_row_stride(R)
-    T = np.zeros((50, rs), np.uint16)
-    T[:, : 2 * R + 2] = np.linspace(0, 65535, 2 * R + 2).astype(np.uint16)
+    T = make_rows(np.tile(np.linspace(0, 65535, 2 * R + 2).astype(np.uint16), (50, 1)), R)
     o = np.empty(50, np.int32)
     enc = np.array([0x12345678, 0x80000000 >> 1], np.uint32).tobytes()   # state only, no renorm words
     assert L.flashgmm_rans_pop_table(enc, len(enc), T.ctypes.data, rs, 50, R, o.ctypes.data) == _lib.ETRUNC
