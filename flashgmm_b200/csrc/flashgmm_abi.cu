@@ -193,14 +193,50 @@ struct flashgmm_ctx {
     std::mutex mu;
     std::vector<std::unique_ptr<Lane>> lanes;   // lane 0 = caller's thread; 1.. = workers
     std::unique_ptr<Pool> pool;
-    int64_t enc_chunk = 1 << 20;
-    int64_t dec_chunk_bytes = 16 << 20;
+    int64_t enc_chunk = 1 << 20, enc_first = 16384;
+    int64_t dec_chunk_bytes = 16 << 20, dec_first = 8192;
     int n_workers = 8;
 };
 
 namespace {
 
 inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+
+// Chunk plan of a stream: (offset, count) in PROCESSING order. Chunks grow
+// geometrically from `first` to `cap` symbols so that the host starts its serial
+// pass after a short first kernel instead of after the whole stream; every offset
+// is a multiple of `first` (itself a multiple of 128), which keeps 128-bit loads
+// aligned. reverse = the encoder's order (last symbols first, small chunks at the tail).
+struct Chunk { int64_t c0, cnt; };
+std::vector<Chunk> plan_chunks(int64_t n, int64_t first, int64_t cap, bool reverse) {
+    std::vector<Chunk> out;
+    if (n <= 0) return out;
+    const int64_t m = n / first, r = n % first;           // whole blocks of `first` symbols + ragged rest
+    if (m == 0) { out.push_back({0, n}); return out; }
+    std::vector<int64_t> blocks;                          // chunk sizes in blocks: 1, 2, 4, ... <= cap/first
+    const int64_t cap_b = std::max<int64_t>(1, cap / first);
+    for (int64_t left = m, b = 1; left > 0; b = std::min(cap_b, b * 2)) {
+        int64_t take = std::min(left, b);
+        blocks.push_back(take);
+        left -= take;
+    }
+    if (!reverse) {
+        int64_t c0 = 0;
+        for (size_t i = 0; i < blocks.size(); ++i) {
+            int64_t cnt = blocks[i] * first + (i + 1 == blocks.size() ? r : 0);
+            out.push_back({c0, cnt});
+            c0 += cnt;
+        }
+    } else {
+        int64_t end = n;
+        for (size_t i = 0; i < blocks.size(); ++i) {
+            int64_t cnt = blocks[i] * first + (i == 0 ? r : 0);
+            out.push_back({end - cnt, cnt});
+            end -= cnt;
+        }
+    }
+    return out;
+}
 
 inline void prof_begin(Slot& S, int kind, double bytes) {
     S.prof_kind = -1;
@@ -285,14 +321,15 @@ int encode_stream(flashgmm_ctx* ctx, Lane& L, flashgmm_stream& s, int mode, int 
     if (!s.bytes && s.bytes_cap) return fail(FLASHGMM_EINVAL, "null output buffer");
     if ((rc = L.init())) return rc;
 
-    const int64_t n = s.n, CH = ctx->enc_chunk;
-    const int64_t nch = (n + CH - 1) / CH;
+    const int64_t n = s.n;
+    const std::vector<Chunk> plan = plan_chunks(n, ctx->enc_first, ctx->enc_chunk, true);
+    const int64_t nch = (int64_t)plan.size();
     L.bb.reset((size_t)(n * 9 / 16) + 64);
     RansEncoder64 enc;
     enc.init(&L.bb);
 
     auto issue = [&](int64_t q) -> int {
-        const int64_t c = nch - 1 - q, c0 = c * CH, cnt = std::min(CH, n - c0);
+        const int64_t c0 = plan[q].c0, cnt = plan[q].cnt;
         Slot& S = L.slot[q % kSlots];
         const int64_t cntp = round_up(cnt, 4);
         CU_TRY(S.d_out.need((size_t)(cntp + 4) * 4));
@@ -321,7 +358,7 @@ int encode_stream(flashgmm_ctx* ctx, Lane& L, flashgmm_stream& s, int mode, int 
     for (int64_t q = 0; q < std::min<int64_t>(kSlots, nch); ++q)
         if ((rc = issue(q))) return rc;
     for (int64_t q = 0; q < nch; ++q) {
-        const int64_t c = nch - 1 - q, c0 = c * CH, cnt = std::min(CH, n - c0);
+        const int64_t c0 = plan[q].c0, cnt = plan[q].cnt;
         Slot& S = L.slot[q % kSlots];
         CU_TRY(cudaEventSynchronize(S.ev));
         prof_collect(S);
@@ -360,10 +397,10 @@ int decode_stream(flashgmm_ctx* ctx, Lane& L, flashgmm_stream& s, int mode, int 
     if ((rc = L.init())) return rc;
 
     const int64_t n = s.n;
-    const int rs = gmm_table_row_stride(R);
-    int64_t CH = ctx->dec_chunk_bytes / (rs * 2);
-    CH = std::max<int64_t>(1024, std::min<int64_t>(CH, 1 << 20)) / 128 * 128;
-    const int64_t nch = (n + CH - 1) / CH;
+    const int rs = table_row_stride(R);
+    const int64_t cap = std::max<int64_t>(128, std::min<int64_t>(ctx->dec_chunk_bytes / (rs * 2), 1 << 20)) / 128 * 128;
+    const std::vector<Chunk> plan = plan_chunks(n, std::min<int64_t>(cap, ctx->dec_first), cap, false);
+    const int64_t nch = (int64_t)plan.size();
 
     int32_t* out_h = s.symbols_out;
     if (mem == FLASHGMM_MEM_DEVICE && n > 0) {
@@ -372,7 +409,7 @@ int decode_stream(flashgmm_ctx* ctx, Lane& L, flashgmm_stream& s, int mode, int 
     }
 
     auto issue = [&](int64_t q) -> int {
-        const int64_t c0 = q * CH, cnt = std::min(CH, n - c0);
+        const int64_t c0 = plan[q].c0, cnt = plan[q].cnt;
         Slot& S = L.slot[q % kSlots];
         const size_t tab_bytes = (size_t)cnt * rs * 2;
         CU_TRY(S.d_out.need(tab_bytes));
@@ -386,7 +423,7 @@ int decode_stream(flashgmm_ctx* ctx, Lane& L, flashgmm_stream& s, int mode, int 
             view = device_view(s, c0);
         }
         prof_begin(S, PROF_TABLE, (48.0 + 2.0 * rs) * (double)cnt);
-        CU_TRY(launch_gmm_cdf_table(view, cnt, mode, R, static_cast<uint16_t*>(S.d_out.p), rs, S.st));
+        CU_TRY(launch_gmm_cdf_table(view, cnt, mode, R, static_cast<uint16_t*>(S.d_out.p), rs, table_has_lut(R), S.st));
         prof_end(S);
         g_launches.fetch_add(1, std::memory_order_relaxed);
         CU_TRY(cudaMemcpyAsync(S.h_out.p, S.d_out.p, tab_bytes, cudaMemcpyDeviceToHost, S.st));
@@ -399,7 +436,7 @@ int decode_stream(flashgmm_ctx* ctx, Lane& L, flashgmm_stream& s, int mode, int 
     for (int64_t q = 0; q < std::min<int64_t>(kSlots, nch); ++q)
         if ((rc = issue(q))) return rc;
     for (int64_t q = 0; q < nch; ++q) {
-        const int64_t c0 = q * CH, cnt = std::min(CH, n - c0);
+        const int64_t c0 = plan[q].c0, cnt = plan[q].cnt;
         Slot& S = L.slot[q % kSlots];
         CU_TRY(cudaEventSynchronize(S.ev));
         prof_collect(S);
@@ -508,7 +545,9 @@ int flashgmm_ctx_create(int device, flashgmm_ctx** out) {
     CU_TRY(cudaFree(0));
     flashgmm_ctx* c = new flashgmm_ctx();
     c->device = device;
-    c->enc_chunk = std::max<long>(4096, env_long("FLASHGMM_ENC_CHUNK", 1 << 20)) / 4 * 4;
+    c->enc_first = std::max<long>(128, env_long("FLASHGMM_ENC_FIRST", 16384)) / 128 * 128;
+    c->enc_chunk = std::max<long>(c->enc_first, env_long("FLASHGMM_ENC_CHUNK", 1 << 20)) / 128 * 128;
+    c->dec_first = std::max<long>(128, env_long("FLASHGMM_DEC_FIRST", 8192)) / 128 * 128;
     c->dec_chunk_bytes = std::max<long>(1 << 16, env_long("FLASHGMM_DEC_CHUNK_BYTES", 16 << 20));
     long hw = (long)std::thread::hardware_concurrency();
     c->n_workers = (int)std::max<long>(1, env_long("FLASHGMM_WORKERS", std::min<long>(16, hw > 1 ? hw - 1 : 1)));
@@ -544,7 +583,7 @@ int flashgmm_gmm_startfreq(flashgmm_ctx* ctx, const int32_t* symbols_d, const fl
     return FLASHGMM_OK;
 }
 
-int flashgmm_gmm_table_row_stride(int32_t R) { return R < 0 ? -1 : gmm_table_row_stride(R); }
+int flashgmm_gmm_table_row_stride(int32_t R) { return R < 0 ? -1 : table_row_stride(R); }
 
 int flashgmm_gmm_cdf_table(flashgmm_ctx* ctx, const float* scales_d, const float* means_d,
                            const float* weights_d, int64_t n, int64_t stride_n, int64_t stride_k,
@@ -553,8 +592,8 @@ int flashgmm_gmm_cdf_table(flashgmm_ctx* ctx, const float* scales_d, const float
     int rc = check_gmm_args(scales_d, means_d, weights_d, n, stride_n, stride_k, mode, FLASHGMM_MEM_DEVICE);
     if (rc) return rc;
     if (R < 0 || R > kMaxTableR) return fail(FLASHGMM_EINVAL, "R outside [0, %d]", kMaxTableR);
-    if (row_stride != gmm_table_row_stride(R))
-        return fail(FLASHGMM_EINVAL, "row_stride must be flashgmm_gmm_table_row_stride(R) = %d", gmm_table_row_stride(R));
+    if (row_stride != table_row_stride(R))
+        return fail(FLASHGMM_EINVAL, "row_stride must be flashgmm_table_row_stride(R) = %d", table_row_stride(R));
     if (n > 0 && !table_d) return fail(FLASHGMM_EINVAL, "null table");
     std::lock_guard<std::mutex> g(ctx->mu);
     CU_TRY(cudaSetDevice(ctx->device));
@@ -562,7 +601,7 @@ int flashgmm_gmm_cdf_table(flashgmm_ctx* ctx, const float* scales_d, const float
     Lane& L = lane_of(ctx, 0);
     if (!st) { if ((rc = L.init())) return rc; st = L.slot[0].st; }
     GmmParamsView v{scales_d, means_d, weights_d, stride_n, stride_k};
-    CU_TRY(launch_gmm_cdf_table(v, n, mode, R, table_d, (int)row_stride, st));
+    CU_TRY(launch_gmm_cdf_table(v, n, mode, R, table_d, (int)row_stride, table_has_lut(R), st));
     g_launches.fetch_add(1, std::memory_order_relaxed);
     if (!stream) CU_TRY(cudaStreamSynchronize(st));
     return FLASHGMM_OK;
@@ -627,7 +666,7 @@ int flashgmm_rans_push_packed(const uint32_t* packed, const int32_t* symbols, in
 
 int flashgmm_rans_pop_table(const uint8_t* encoded, size_t encoded_len, const uint16_t* table,
                             int64_t row_stride, int64_t n, int32_t R, int32_t* symbols_out) {
-    if (!encoded || n < 0 || (n > 0 && (!table || !symbols_out)) || R < 0 || row_stride != gmm_table_row_stride(R))
+    if (!encoded || n < 0 || (n > 0 && (!table || !symbols_out)) || R < 0 || row_stride != table_row_stride(R))
         return fail(FLASHGMM_EINVAL, "bad argument");
     RansDecoder64 dec;
     dec.init(encoded, encoded_len);

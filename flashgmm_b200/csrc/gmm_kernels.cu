@@ -113,81 +113,110 @@ gmm_startfreq_scalar_kernel(const int32_t* __restrict__ sym, GmmParamsView p, in
 }
 
 // ---- decode side: quantised CDF rows ----
-// Row layout (uint16 elements), R = search radius, W = 2R+2:
+// Row layout (uint16 elements), R = search radius, W = 2R+2 entries:
 //   [0, W)            T[j] = q16(cdf(j - R - 0.5))
 //   [W]               1 if T is not non-decreasing (host then replays the reference's search)
 //   (W, lut_off)      zero padding, lut_off = round_up(W+1, 8)
-//   [lut_off, +32)    jump table: lut[b] = max{ j in [0,2R] : T[j] <= b*2048 } (0 if none), so the
-//                     host starts its scan for cum at lut[cum >> 11] instead of at -R.
-constexpr int kTabThreads = 128;   // symbols per block
-constexpr int kTabTile = 64;       // uint16 entries per tile (32 words)
-constexpr int kTabTileWords = kTabTile / 2;
+//   [lut_off, +32)    only when the host asks for it (long rows): jump table,
+//                     lut[b] = max{ j in [0,2R] : T[j] <= b*2048 } (0 if none).
+//
+// Work decomposition: one thread per PAIR of adjacent entries (one 32-bit word of
+// the row), so a stream of n symbols exposes n*(R+1) independent work items -- small
+// streams (12 288 symbols in ELIC's first groups) still fill 148 SMs -- and the word
+// index maps linearly onto the global address: stores are coalesced by construction.
+// A CTA owns S consecutive symbols; their 12 parameters are staged once in shared
+// memory (coalesced plane reads), the row image is assembled there so that the
+// monotonicity flag and the jump table can be derived, then streamed out.
+constexpr int kRowThreads = 128;
 constexpr int kLutBuckets = 32;
 constexpr int kLutShift = 11;
 
 template <int MODE>
-__global__ void __launch_bounds__(kTabThreads)
-gmm_cdf_table_kernel(GmmParamsView p, int64_t n, int R, uint16_t* __restrict__ table, int row_stride) {
-    __shared__ uint32_t tile[kTabThreads][kTabTileWords + 1];
-    __shared__ uint32_t lut_s[kTabThreads][kLutBuckets / 2 + 1];
-    const int64_t row0 = (int64_t)blockIdx.x * kTabThreads;
-    const int64_t i = row0 + threadIdx.x;
-    const bool live = i < n;
-    float mu[4] = {0, 0, 0, 0}, sg[4] = {1, 1, 1, 1}, w[4] = {0, 0, 0, 0};
-    if (live) load_generic(p, i, mu, sg, w);
+__global__ void __launch_bounds__(kRowThreads)
+gmm_cdf_rows_kernel(GmmParamsView p, int64_t n, int R, uint32_t* __restrict__ table32, int row_words,
+                    int lut_off, int S) {
+    extern __shared__ uint32_t smem_u32[];
+    float* prm = reinterpret_cast<float*>(smem_u32);       // [12][S]: sg[4], mu[4], w[4]
+    uint32_t* tile = smem_u32 + 12 * S;                    // [S][row_words]
+    uint32_t* bad = tile + (size_t)S * row_words;          // [S]
 
+    const int64_t row0 = (int64_t)blockIdx.x * S;
+    const int live = (int)min((int64_t)S, n - row0);
     const int W = 2 * R + 2;
-    const int lut_off = (W + 1 + 7) & ~7;
-    uint32_t prev = 0, nonmono = 0;
-    int cn = 0;                                   // next jump-table bucket to fill
-    uint16_t* my_lut = reinterpret_cast<uint16_t*>(lut_s[threadIdx.x]);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    uint32_t* tab32 = reinterpret_cast<uint32_t*>(table);
-    const int row_words = row_stride >> 1;
 
-    for (int j0 = 0; j0 < lut_off; j0 += kTabTile) {
-        if (live) {
-#pragma unroll 2
-            for (int jj = 0; jj < kTabTile; jj += 2) {
-                uint32_t e[2];
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    int j = j0 + jj + h;
-                    uint32_t c = 0;
-                    if (j < W) {
-                        // v - 0.5 with v = j - R; identical to (v-1) - 0.5 + 1.0 for |v| < 2^22
-                        c = gmm_q16<MODE>(__fsub_rn((float)(j - R), 0.5f), mu, sg, w);
-                        nonmono |= (c < prev);
-                        prev = c;
-                        if (j < W - 1) {          // candidates are j in [0, 2R]
-                            while (cn < kLutBuckets && (uint32_t)(cn << kLutShift) < c) {
-                                my_lut[cn++] = (uint16_t)(j > 0 ? j - 1 : 0);
-                            }
-                        }
-                    } else if (j == W) {
-                        c = nonmono;
-                    }
-                    e[h] = c;
-                }
-                tile[threadIdx.x][jj >> 1] = e[0] | (e[1] << 16);
-            }
+    for (int idx = threadIdx.x; idx < 12 * S; idx += kRowThreads) {
+        const int plane = idx / S, s = idx - plane * S;
+        float v = plane < 4 ? 1.0f : 0.0f;
+        if (s < live) {
+            const int k = plane & 3;
+            const float* base = plane < 4 ? p.scales : (plane < 8 ? p.means : p.weights);
+            v = __ldg(base + (row0 + s) * p.stride_n + k * p.stride_k);
         }
-        __syncthreads();
-        // coalesced write-out: one warp per row segment (<=128 B)
-        const int wbase = j0 >> 1;
-        for (int r = warp; r < kTabThreads; r += kTabThreads / 32) {
-            int64_t row = row0 + r;
-            if (row < n && wbase + lane < (lut_off >> 1))
-                tab32[row * row_words + wbase + lane] = tile[r][lane];
+        prm[idx] = v;
+    }
+    for (int s = threadIdx.x; s < S; s += kRowThreads) bad[s] = 0;
+    __syncthreads();
+
+    const int items = live * row_words;
+    const int step_s = kRowThreads / row_words, step_w = kRowThreads - step_s * row_words;
+    {
+        int s = threadIdx.x / row_words, wd = threadIdx.x - s * row_words;
+        for (int id = threadIdx.x; id < items; id += kRowThreads) {
+            const int j = 2 * wd;
+            uint32_t e0 = 0, e1 = 0;
+            if (j < W) {                                   // W is even: j < W implies j + 1 < W
+                float mu[4], sg[4], w[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    sg[k] = prm[k * S + s];
+                    mu[k] = prm[(4 + k) * S + s];
+                    w[k] = prm[(8 + k) * S + s];
+                }
+                // v - 0.5 with v = j - R; identical to (v-1) - 0.5 + 1.0 for |v| < 2^22
+                e0 = gmm_q16<MODE>(__fsub_rn((float)(j - R), 0.5f), mu, sg, w);
+                e1 = gmm_q16<MODE>(__fsub_rn((float)(j + 1 - R), 0.5f), mu, sg, w);
+                if (e1 < e0) atomicOr(&bad[s], 1u);
+            }
+            tile[id] = e0 | (e1 << 16);
+            s += step_s; wd += step_w;
+            if (wd >= row_words) { wd -= row_words; ++s; }
+        }
+    }
+    __syncthreads();
+    {   // pairs that straddle two words
+        int s = threadIdx.x / row_words, wd = threadIdx.x - s * row_words;
+        for (int id = threadIdx.x; id < items; id += kRowThreads) {
+            if (2 * wd + 2 < W && (tile[id + 1] & 0xffffu) < (tile[id] >> 16)) atomicOr(&bad[s], 1u);
+            s += step_s; wd += step_w;
+            if (wd >= row_words) { wd -= row_words; ++s; }
+        }
+    }
+    __syncthreads();
+    if (lut_off >= 0) {
+        for (int idx = threadIdx.x; idx < live * kLutBuckets; idx += kRowThreads) {
+            const int s = idx / kLutBuckets, b = idx - s * kLutBuckets;
+            uint16_t* row16 = reinterpret_cast<uint16_t*>(tile + (size_t)s * row_words);
+            const uint32_t key = (uint32_t)b << kLutShift;
+            int lo = 0, hi = 2 * R + 1;                    // count of candidates j in [0,2R] with T[j] <= key
+            while (lo < hi) {
+                int mid = (lo + hi) >> 1;
+                if (row16[mid] <= key) lo = mid + 1; else hi = mid;
+            }
+            row16[lut_off + b] = (uint16_t)(lo > 0 ? lo - 1 : 0);
         }
         __syncthreads();
     }
-    if (live) while (cn < kLutBuckets) my_lut[cn++] = (uint16_t)(2 * R);
-    __syncthreads();
-    // jump tables: 16 words per row, two rows per warp pass
-    for (int r = warp * 2 + (lane >> 4); r < kTabThreads; r += (kTabThreads / 32) * 2) {
-        int64_t row = row0 + r;
-        if (row < n) tab32[row * row_words + (lut_off >> 1) + (lane & 15)] = lut_s[r][lane & 15];
+    {
+        uint32_t* dst = table32 + row0 * row_words;
+        int s = threadIdx.x / row_words, wd = threadIdx.x - s * row_words;
+        const int flag_word = W >> 1;
+        for (int id = threadIdx.x; id < items; id += kRowThreads) {
+            uint32_t v = tile[id];
+            if (wd == flag_word) v |= bad[s];
+            __stcs(dst + id, v);
+            s += step_s; wd += step_w;
+            if (wd >= row_words) { wd -= row_words; ++s; }
+        }
     }
 }
 
@@ -213,15 +242,20 @@ template <int MODE>
 static cudaError_t launch_startfreq_mode(const int32_t* sym, const GmmParamsView& p, int64_t n,
                                          uint32_t* out, uint32_t* bypass_flag, cudaStream_t st) {
     if (n <= 0) return cudaSuccess;
-    switch (gmm_layout_of(p, sym, out)) {
+    int layout = gmm_layout_of(p, sym, out);
+    // Small streams: 4 symbols per thread would leave most SMs idle (12 288 symbols = 12 CTAs);
+    // one symbol per thread in 128-thread CTAs exposes 4x the parallelism and the
+    // 32-bit plane loads are still coalesced.
+    if (layout == 0 && n < 148LL * 2 * kSfThreads * 4) layout = 2;
+    switch (layout) {
     case 0:
         gmm_startfreq_kmajor4_kernel<MODE><<<grid_for((n + 3) / 4, kSfThreads), kSfThreads, 0, st>>>(sym, p, n, out, bypass_flag);
         break;
     case 1:
-        gmm_startfreq_scalar_kernel<MODE, true><<<grid_for(n, kSfThreads), kSfThreads, 0, st>>>(sym, p, n, out, bypass_flag);
+        gmm_startfreq_scalar_kernel<MODE, true><<<grid_for(n, 128), 128, 0, st>>>(sym, p, n, out, bypass_flag);
         break;
     default:
-        gmm_startfreq_scalar_kernel<MODE, false><<<grid_for(n, kSfThreads), kSfThreads, 0, st>>>(sym, p, n, out, bypass_flag);
+        gmm_startfreq_scalar_kernel<MODE, false><<<grid_for(n, 128), 128, 0, st>>>(sym, p, n, out, bypass_flag);
     }
     return cudaGetLastError();
 }
@@ -236,23 +270,41 @@ cudaError_t launch_gmm_startfreq(const int32_t* sym, const GmmParamsView& p, int
 }
 
 int gmm_table_lut_offset(int R) { return ((2 * R + 3) + 7) & ~7; }
-int gmm_table_row_stride(int R) { return gmm_table_lut_offset(R) + kLutBuckets; }
+
+namespace {
+constexpr size_t kRowSmemBudget = 96 * 1024;
+
+template <int MODE>
+cudaError_t launch_rows_mode(const GmmParamsView& p, int64_t n, int R, uint16_t* table, int row_stride,
+                             bool with_lut, cudaStream_t st) {
+    const int row_words = row_stride >> 1;
+    const size_t per_sym = (size_t)(12 + row_words + 1) * 4;
+    int64_t S = n / (148 * 4);                     // enough CTAs to cover the SMs a few times
+    S = S < 8 ? 8 : (S > 64 ? 64 : S);
+    const int64_t fit = (int64_t)(kRowSmemBudget / per_sym);
+    if (S > fit) S = fit;
+    if (S < 1) return cudaErrorInvalidValue;
+    const int64_t blocks = (n + S - 1) / S;
+    const size_t smem = (size_t)S * per_sym;
+    if (smem > 48 * 1024) {   // long rows only (R > ~750): opt in to large dynamic shared memory on this device
+        cudaError_t e = cudaFuncSetAttribute(gmm_cdf_rows_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)kRowSmemBudget);
+        if (e != cudaSuccess) return e;
+    }
+    gmm_cdf_rows_kernel<MODE><<<(unsigned)blocks, kRowThreads, smem, st>>>(
+        p, n, R, reinterpret_cast<uint32_t*>(table), row_words, with_lut ? gmm_table_lut_offset(R) : -1, (int)S);
+    return cudaGetLastError();
+}
+}  // namespace
 
 cudaError_t launch_gmm_cdf_table(const GmmParamsView& p, int64_t n, int mode, int R, uint16_t* table,
-                                 int row_stride, cudaStream_t st) {
+                                 int row_stride, bool with_lut, cudaStream_t st) {
     if (n <= 0) return cudaSuccess;
-    int64_t blocks = (n + kTabThreads - 1) / kTabThreads;
     switch (mode) {
-    case MODE_AS:
-        gmm_cdf_table_kernel<MODE_AS><<<(unsigned)blocks, kTabThreads, 0, st>>>(p, n, R, table, row_stride);
-        break;
-    case MODE_LOGISTIC:
-        gmm_cdf_table_kernel<MODE_LOGISTIC><<<(unsigned)blocks, kTabThreads, 0, st>>>(p, n, R, table, row_stride);
-        break;
-    default:
-        gmm_cdf_table_kernel<MODE_POLYA><<<(unsigned)blocks, kTabThreads, 0, st>>>(p, n, R, table, row_stride);
+    case MODE_AS: return launch_rows_mode<MODE_AS>(p, n, R, table, row_stride, with_lut, st);
+    case MODE_LOGISTIC: return launch_rows_mode<MODE_LOGISTIC>(p, n, R, table, row_stride, with_lut, st);
+    default: return launch_rows_mode<MODE_POLYA>(p, n, R, table, row_stride, with_lut, st);
     }
-    return cudaGetLastError();
 }
 
 }  // namespace flashgmm

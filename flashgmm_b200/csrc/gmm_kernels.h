@@ -23,11 +23,12 @@ cudaError_t launch_gmm_startfreq(const int32_t* sym, const GmmParamsView& p, int
                                  uint32_t* out, uint32_t* bypass_flag, cudaStream_t st);
 
 // Decode-table row for search radius R (uint16 elements): 2R+2 CDF entries, 1 flag
-// slot, zero padding up to lut_offset (multiple of 8), then a 32-entry jump table.
+// slot, zero padding up to lut_offset (multiple of 8), then -- if with_lut -- a
+// 32-entry jump table. The row stride is decided by the host search code
+// (rans_host.hpp: table_row_stride / table_has_lut).
 int gmm_table_lut_offset(int R);
-int gmm_table_row_stride(int R);
 
 cudaError_t launch_gmm_cdf_table(const GmmParamsView& p, int64_t n, int mode, int R, uint16_t* table,
-                                 int row_stride, cudaStream_t st);
+                                 int row_stride, bool with_lut, cudaStream_t st);
 
 }  // namespace flashgmm

@@ -192,6 +192,13 @@ struct RansDecoder64 {
 constexpr int kLutShift = 11;
 constexpr int kLutBuckets = 32;
 inline int table_lut_offset(int32_t R) { return ((2 * R + 3) + 7) & ~7; }
+// Short rows (<= 64 candidates) are searched whole with AVX2 and carry no jump table.
+#if defined(__AVX2__)
+inline bool table_has_lut(int32_t R) { return 2 * R + 1 > 64; }
+#else
+inline bool table_has_lut(int32_t) { return true; }
+#endif
+inline int table_row_stride(int32_t R) { return table_lut_offset(R) + (table_has_lut(R) ? kLutBuckets : 0); }
 
 // Per-call search plan: short rows are counted whole with AVX2 (no dependent jump-table
 // load, no data-dependent branch); long rows start from the jump table.
@@ -203,7 +210,7 @@ struct SearchPlan {
     explicit SearchPlan(int32_t r) : R(r), lut_off(table_lut_offset(r)) {
         const int cand = 2 * r + 1;
 #if defined(__AVX2__)
-        if (cand <= 64) {
+        if (!table_has_lut(r)) {
             nvec = (cand + 15) / 16;
             for (int v = 0; v < nvec; ++v) {
                 int lanes = cand - 16 * v;

@@ -24,6 +24,7 @@ def main():
     enc = ans.RansEncoder()
     dec = ans.RansDecoder()
     stdin, stdout = sys.stdin.buffer, sys.stdout.buffer
+    store = {}
 
     def params(kw):
         out = []
@@ -65,6 +66,23 @@ def main():
                                         [list(map(int, r)) for r in kw["cdfs"]],
                                         list(map(int, kw["cdf_sizes"])), list(map(int, kw["offsets"])))
             return np.asarray(o, np.int32)
+        if op == "put":           # keep a stream resident in the worker (bench: no pickling inside a step)
+            store[kw["key"]] = (torch.from_numpy(np.ascontiguousarray(kw["symbols"], np.int32)), params(kw),
+                                int(kw["max_bs_value"]))
+            return True
+        if op == "roundtrip":     # encode + decode every stored stream named in `keys`
+            ok, te, td = True, 0.0, 0.0
+            for key in kw["keys"]:
+                sym, (sc, mu, w), R = store[key]
+                t0 = time.perf_counter()
+                b = enc.encode_with_indexes_gmm(sym, sc, mu, w, R)
+                t1 = time.perf_counter()
+                o = dec.decode_with_indexes_gmm(b, sc, mu, w, R)
+                t2 = time.perf_counter()
+                ok = ok and bool(torch.equal(o, sym))
+                te += t1 - t0
+                td += t2 - t1
+            return ok, te, td
         if op == "ping":
             return "pong"
         raise ValueError(op)
