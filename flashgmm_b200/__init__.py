@@ -10,3 +10,5 @@ __version__ = "0.1.0"
 from . import _lib  # noqa: F401
 from .ans import (RansDecoder, RansEncoder, get_approx_mode, gmm_decode, gmm_encode,  # noqa: F401
                   set_approx_mode, table_decode, table_encode)
+from .entropy_models import GaussianMixtureConditional, LowerBound  # noqa: F401,E402
+from .latent_codecs import GaussianMixtureConditionalLatentCodec  # noqa: F401,E402

@@ -46,6 +46,10 @@ _SIGS = {
     "flashgmm_gmm_decode": (C.c_int, [_vp, _vp, _sz, _vp, _vp, _vp, _i64, _i64, _i64, C.c_int, C.c_int, _i32, _vp]),
     "flashgmm_gmm_encode_batch": (C.c_int, [_vp, C.POINTER(Stream), C.c_int, C.c_int, C.c_int]),
     "flashgmm_gmm_decode_batch": (C.c_int, [_vp, C.POINTER(Stream), C.c_int, C.c_int, C.c_int]),
+    "flashgmm_gmm_likelihood_fwd": (C.c_int, [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _i64, _i64, C.c_int, C.c_float,
+                                              C.c_float, _vp, _vp, _vp]),
+    "flashgmm_gmm_likelihood_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, C.c_int, C.c_float,
+                                              C.c_float, _vp, _vp, _vp, _vp, _vp]),
     "flashgmm_rans_push_packed": (C.c_int, [_vp, _vp, _i64, _vp, _sz, C.POINTER(_sz)]),
     "flashgmm_rans_pop_table": (C.c_int, [_vp, _sz, _vp, _i64, _i64, _i32, _vp]),
     "flashgmm_rans_encode_table": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _sz, C.POINTER(_sz)]),

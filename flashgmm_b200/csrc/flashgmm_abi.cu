@@ -642,6 +642,62 @@ int flashgmm_gmm_decode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     return run_batch(ctx, streams, n_streams, mode, mem, decode_stream);
 }
 
+// ---- likelihood ----
+static int lk_stream(flashgmm_ctx* ctx, void* stream, cudaStream_t* st) {
+    *st = static_cast<cudaStream_t>(stream);
+    if (*st) return FLASHGMM_OK;
+    Lane& L = lane_of(ctx, 0);
+    int rc = L.init();
+    if (rc) return rc;
+    *st = L.slot[0].st;
+    return FLASHGMM_OK;
+}
+
+int flashgmm_gmm_likelihood_fwd(flashgmm_ctx* ctx, const float* x_d, const float* noise_d, int quant,
+                                const float* scales_d, const float* means_d, const float* weights_d,
+                                int64_t B, int64_t plane, int K, float scale_bound, float lik_bound,
+                                float* y_out_d, float* lik_out_d, void* stream) {
+    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
+    if (B < 0 || plane < 0) return fail(FLASHGMM_EINVAL, "negative size");
+    if (K < 1 || K > 8) return fail(FLASHGMM_EINVAL, "K must be in [1, 8], got %d", K);
+    if (quant < 0 || quant > 2) return fail(FLASHGMM_EINVAL, "quant must be 0, 1 or 2");
+    if (B * plane > 0 && (!x_d || !scales_d || !means_d || !weights_d || !y_out_d || !lik_out_d || (quant == 1 && !noise_d)))
+        return fail(FLASHGMM_EINVAL, "null pointer");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CU_TRY(cudaSetDevice(ctx->device));
+    cudaStream_t st;
+    int rc = lk_stream(ctx, stream, &st);
+    if (rc) return rc;
+    CU_TRY(launch_gmm_likelihood_fwd(x_d, noise_d, quant, scales_d, means_d, weights_d, B, plane, K, scale_bound,
+                                     lik_bound, y_out_d, lik_out_d, st));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (!stream) CU_TRY(cudaStreamSynchronize(st));
+    return FLASHGMM_OK;
+}
+
+int flashgmm_gmm_likelihood_bwd(flashgmm_ctx* ctx, const float* y_d, const float* scales_d,
+                                const float* means_d, const float* weights_d, const float* grad_lik_d,
+                                int64_t B, int64_t plane, int K, float scale_bound, float lik_bound,
+                                float* grad_y_d, float* grad_scales_d, float* grad_means_d,
+                                float* grad_weights_d, void* stream) {
+    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
+    if (B < 0 || plane < 0) return fail(FLASHGMM_EINVAL, "negative size");
+    if (K < 1 || K > 8) return fail(FLASHGMM_EINVAL, "K must be in [1, 8], got %d", K);
+    if (B * plane > 0 && (!y_d || !scales_d || !means_d || !weights_d || !grad_lik_d || !grad_y_d || !grad_scales_d ||
+                          !grad_means_d || !grad_weights_d))
+        return fail(FLASHGMM_EINVAL, "null pointer");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CU_TRY(cudaSetDevice(ctx->device));
+    cudaStream_t st;
+    int rc = lk_stream(ctx, stream, &st);
+    if (rc) return rc;
+    CU_TRY(launch_gmm_likelihood_bwd(y_d, scales_d, means_d, weights_d, grad_lik_d, B, plane, K, scale_bound, lik_bound,
+                                     grad_y_d, grad_scales_d, grad_means_d, grad_weights_d, st));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (!stream) CU_TRY(cudaStreamSynchronize(st));
+    return FLASHGMM_OK;
+}
+
 // ---- host-only halves ----
 static int emit(BackBuffer& bb, uint8_t* out, size_t cap, size_t* out_len) {
     *out_len = bb.bytes();

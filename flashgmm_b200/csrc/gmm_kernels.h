@@ -31,4 +31,16 @@ int gmm_table_lut_offset(int R);
 cudaError_t launch_gmm_cdf_table(const GmmParamsView& p, int64_t n, int mode, int R, uint16_t* table,
                                  int row_stride, bool with_lut, cudaStream_t st);
 
+// GaussianMixtureConditional likelihood (gmm_likelihood.cu). x / y / lik / grad are
+// (B, plane) contiguous; parameters are (B, K, plane) contiguous (plane = M*H*W).
+// quant: 0 = y = x, 1 = y = x + noise, 2 = y = rint(x).
+cudaError_t launch_gmm_likelihood_fwd(const float* x, const float* noise, int quant, const float* sc,
+                                      const float* mu, const float* w, int64_t B, int64_t plane, int K,
+                                      float scale_bound, float lik_bound, float* y_out, float* lik_out,
+                                      cudaStream_t st);
+cudaError_t launch_gmm_likelihood_bwd(const float* y, const float* sc, const float* mu, const float* w,
+                                      const float* grad, int64_t B, int64_t plane, int K, float scale_bound,
+                                      float lik_bound, float* gy, float* gsc, float* gmu, float* gw,
+                                      cudaStream_t st);
+
 }  // namespace flashgmm

@@ -123,6 +123,31 @@ int flashgmm_gmm_encode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
 int flashgmm_gmm_decode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode,
                               int mem);
 
+/* ---- training / evaluation likelihood (device pointers, asynchronous on `stream`) ---- */
+
+/* GaussianMixtureConditional.forward, EM:792-808 (+ _likelihood EM:774-790, 720-737,
+ * _standardized_cumulative EM:674-678, quantize EM:157-182, LowerBound ops/bound_ops.py:36-42).
+ *   x, noise, y_out, lik_out : (B, M*HW) float32 contiguous
+ *   scales, means, weights   : (B, K, M*HW) float32 contiguous -- the reference's
+ *                              (B, K*M, H, W) tensors, component k of channel c at channel k*M + c
+ *   quant : 0 y = x | 1 y = x + noise (training "noise") | 2 y = round-half-even(x) ("dequantize")
+ *   scale_bound (0.11) and lik_bound (1e-9; <= 0 disables) are the two LowerBounds.
+ * K in [1, 8]. Contract: 1e-5 relative against the reference's fp32 result. */
+int flashgmm_gmm_likelihood_fwd(flashgmm_ctx* ctx, const float* x_d, const float* noise_d, int quant,
+                                const float* scales_d, const float* means_d, const float* weights_d,
+                                int64_t B, int64_t plane, int K, float scale_bound, float lik_bound,
+                                float* y_out_d, float* lik_out_d, void* stream);
+
+/* Backward of the above through the likelihood output: grad_lik -> grad_y (add to the
+ * incoming grad of y_out for quant 0/1; round has zero gradient), grad_scales,
+ * grad_means, grad_weights, with LowerBound's custom gradient on both bounds
+ * (ops/bound_ops.py:40-42). y_d is the forward's y_out. */
+int flashgmm_gmm_likelihood_bwd(flashgmm_ctx* ctx, const float* y_d, const float* scales_d,
+                                const float* means_d, const float* weights_d, const float* grad_lik_d,
+                                int64_t B, int64_t plane, int K, float scale_bound, float lik_bound,
+                                float* grad_y_d, float* grad_scales_d, float* grad_means_d,
+                                float* grad_weights_d, void* stream);
+
 /* ---- host-only halves (no GPU): the serial rANS recurrence ---- */
 
 /* Push packed (start|freq<<16, freq==0 = bypass -> needs symbols[i]) records:
