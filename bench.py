@@ -359,6 +359,46 @@ def kernel_microbench(torch, synth, L, _lib, dev, mode, n=1 << 24, iters=10):
         by = (48 + 2 * rs) * m
         res["gmm_cdf_rows"] = {"n": m, "R": R, "ms": round(ms, 4), "gsym_s": round(m / ms / 1e6, 3),
                                "gb_s": round(by / ms / 1e6, 1), "hbm_frac": round(by / ms / 1e6 / peak, 4)}
+    del tab, out
+    # single-stream (reference-compatible) vs interleaved (opt-in format) on the same 16 Mi symbols
+    import ctypes as C
+
+    from flashgmm_b200 import ans, ileave
+    Rs = int(sym.abs().max().item()) + 2
+    t0 = time.perf_counter()
+    single = ans.gmm_encode(sym, sg, mu, w, mode)
+    t1 = time.perf_counter()
+    dec = ans.gmm_decode(single, sg, mu, w, Rs, mode)
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    assert torch.equal(dec, sym)
+    res["single_stream"] = {"bytes": len(single), "encode_ms": round(1e3 * (t1 - t0), 2), "decode_ms": round(1e3 * (t2 - t1), 2),
+                            "encode_msym_s": round(n / (t1 - t0) / 1e6, 1), "decode_msym_s": round(n / (t2 - t1) / 1e6, 1),
+                            "note": "one stream = one host thread for the serial rANS recurrence"}
+    blob = ileave.encode(sym, sg, mu, w, Rs, mode)            # warm-up (buffers)
+    assert torch.equal(ileave.decode(blob, sg, mu, w), sym)
+    L.flashgmm_profile_reset()
+    L.flashgmm_profile_enable(1)
+    reps = 3
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        blob = ileave.encode(sym, sg, mu, w, Rs, mode)
+    t1 = time.perf_counter()
+    for _ in range(reps):
+        ileave.decode(blob, sg, mu, w)
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    L.flashgmm_profile_enable(0)
+    il = {"bytes": len(blob), "size_vs_single": round(len(blob) / len(single), 4), "segment_log2": ileave.info(blob)["segment_log2"],
+          "encode_call_ms": round(1e3 * (t1 - t0) / reps, 3), "decode_call_ms": round(1e3 * (t2 - t1) / reps, 3)}
+    for kind, name in ((2, "encode"), (3, "decode")):
+        msv, nl, by = C.c_double(), C.c_uint64(), C.c_double()
+        L.flashgmm_profile_read(kind, C.byref(msv), C.byref(nl), C.byref(by))
+        k_ms = msv.value / max(1, nl.value)
+        il[f"{name}_kernel_ms"] = round(k_ms, 4)
+        il[f"{name}_kernel_gsym_s"] = round(n / k_ms / 1e6, 2) if k_ms > 0 else None
+        il[f"{name}_hbm_frac"] = round(52 * n / k_ms / 1e6 / peak, 4) if k_ms > 0 else None
+    res["interleaved"] = il
     return res
 
 

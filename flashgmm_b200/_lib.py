@@ -46,6 +46,12 @@ _SIGS = {
     "flashgmm_gmm_decode": (C.c_int, [_vp, _vp, _sz, _vp, _vp, _vp, _i64, _i64, _i64, C.c_int, C.c_int, _i32, _vp]),
     "flashgmm_gmm_encode_batch": (C.c_int, [_vp, C.POINTER(Stream), C.c_int, C.c_int, C.c_int]),
     "flashgmm_gmm_decode_batch": (C.c_int, [_vp, C.POINTER(Stream), C.c_int, C.c_int, C.c_int]),
+    "flashgmm_gmm_ileave_max_bytes": (_sz, [_i64, C.c_int]),
+    "flashgmm_gmm_ileave_encode": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, C.c_int, C.c_int, _i32, C.c_int,
+                                             _vp, _sz, C.POINTER(_sz)]),
+    "flashgmm_gmm_ileave_info": (C.c_int, [_vp, _sz, C.POINTER(_i64), C.POINTER(C.c_int), C.POINTER(_i32),
+                                           C.POINTER(C.c_int)]),
+    "flashgmm_gmm_ileave_decode": (C.c_int, [_vp, _vp, _sz, _vp, _vp, _vp, _i64, _i64, _i64, C.c_int, _vp]),
     "flashgmm_gmm_likelihood_fwd": (C.c_int, [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _i64, _i64, C.c_int, C.c_float,
                                               C.c_float, _vp, _vp, _vp]),
     "flashgmm_gmm_likelihood_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, C.c_int, C.c_float,

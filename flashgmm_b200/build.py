@@ -26,6 +26,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-O3,-fno-strict
 # contraction off on top of the explicit _rn intrinsics; host-heavy TUs get AVX2.
 UNITS = [
     ("gmm_kernels.cu", ["-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false"]),
+    ("gmm_ileave.cu", ["-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false"]),
     ("gmm_likelihood.cu", ["-Xptxas", "-v"]),
     ("flashgmm_abi.cu", ["-Xcompiler", "-march=x86-64-v3"]),
 ]

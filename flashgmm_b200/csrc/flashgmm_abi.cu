@@ -34,12 +34,12 @@ std::atomic<uint64_t> g_launches{0};
 
 // Optional per-kernel timing (bench.py's live roofline): CUDA events around each
 // launch on the launching stream, read back when the chunk is consumed.
-enum { PROF_STARTFREQ = 0, PROF_TABLE = 1, PROF_KINDS = 2 };
+enum { PROF_STARTFREQ = 0, PROF_TABLE = 1, PROF_IL_ENC = 2, PROF_IL_DEC = 3, PROF_KINDS = 4 };
 std::atomic<int> g_prof_on{0};
 std::mutex g_prof_mu;
-double g_prof_ms[PROF_KINDS] = {0, 0};
-double g_prof_bytes[PROF_KINDS] = {0, 0};
-uint64_t g_prof_launches[PROF_KINDS] = {0, 0};
+double g_prof_ms[PROF_KINDS] = {};
+double g_prof_bytes[PROF_KINDS] = {};
+uint64_t g_prof_launches[PROF_KINDS] = {};
 
 int fail(int code, const char* fmt, ...) {
     char buf[512];
@@ -196,6 +196,9 @@ struct flashgmm_ctx {
     int64_t enc_chunk = 1 << 20, enc_first = 16384;
     int64_t dec_chunk_bytes = 16 << 20, dec_first = 8192;
     int n_workers = 8;
+    // interleaved coder (whole-stream buffers, lane 0's first stream)
+    DevBuf il_scratch, il_segw, il_out, il_err;
+    PinBuf il_host;
 };
 
 namespace {
@@ -519,7 +522,7 @@ void flashgmm_profile_reset(void) {
 }
 
 int flashgmm_profile_read(int kind, double* total_ms, uint64_t* launches, double* algorithmic_bytes) {
-    if (kind < 0 || kind >= PROF_KINDS) return fail(FLASHGMM_EINVAL, "kind must be 0 (startfreq) or 1 (cdf_table)");
+    if (kind < 0 || kind >= PROF_KINDS) return fail(FLASHGMM_EINVAL, "kind must be 0 (startfreq), 1 (cdf_table), 2 (ileave encode) or 3 (ileave decode)");
     std::lock_guard<std::mutex> g(g_prof_mu);
     if (total_ms) *total_ms = g_prof_ms[kind];
     if (launches) *launches = g_prof_launches[kind];
@@ -561,6 +564,8 @@ void flashgmm_ctx_destroy(flashgmm_ctx* ctx) {
     ctx->pool.reset();
     cudaSetDevice(ctx->device);
     for (auto& l : ctx->lanes) l->destroy();
+    ctx->il_scratch.release(); ctx->il_segw.release(); ctx->il_out.release(); ctx->il_err.release();
+    ctx->il_host.release();
     delete ctx;
 }
 
@@ -640,6 +645,147 @@ int flashgmm_gmm_encode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
 
 int flashgmm_gmm_decode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem) {
     return run_batch(ctx, streams, n_streams, mode, mem, decode_stream);
+}
+
+// ---- interleaved multi-lane rANS ----
+static int il_seg_log2(int v) { return v == 0 ? 13 : v; }
+
+size_t flashgmm_gmm_ileave_max_bytes(int64_t n, int segment_log2) {
+    const int sl = il_seg_log2(segment_log2);
+    if (n < 0 || sl < 10 || sl > 16) return 0;
+    const size_t n_seg = (size_t)((n + ((int64_t)1 << sl) - 1) >> sl);
+    return 32 + 4 * (n_seg + 1) + n_seg * 2 * (size_t)gmm_ileave_scratch_words(sl);
+}
+
+int flashgmm_gmm_ileave_info(const uint8_t* enc, size_t len, int64_t* n, int* mode, int32_t* R, int* segment_log2) {
+    if (!enc || len < 36) return fail(FLASHGMM_ETRUNC, "interleaved container shorter than its header");
+    if (memcmp(enc, "FGIL", 4) != 0 || enc[4] != 1) return fail(FLASHGMM_EINVAL, "not a FGIL v1 container");
+    int64_t hn; int32_t hR; uint32_t nseg; uint64_t pay;
+    memcpy(&hn, enc + 8, 8); memcpy(&hR, enc + 16, 4); memcpy(&nseg, enc + 20, 4); memcpy(&pay, enc + 24, 8);
+    const int sl = enc[6];
+    if (enc[5] > 2 || sl < 10 || sl > 16 || hn < 0 || hR < 0 || (uint64_t)((hn + ((int64_t)1 << sl) - 1) >> sl) != nseg)
+        return fail(FLASHGMM_EINVAL, "corrupt FGIL header");
+    if (len < 32 + 4 * ((size_t)nseg + 1) + pay) return fail(FLASHGMM_ETRUNC, "interleaved container truncated");
+    if (n) *n = hn;
+    if (mode) *mode = enc[5];
+    if (R) *R = hR;
+    if (segment_log2) *segment_log2 = sl;
+    return FLASHGMM_OK;
+}
+
+int flashgmm_gmm_ileave_encode(flashgmm_ctx* ctx, const int32_t* symbols, const float* scales,
+                               const float* means, const float* weights, int64_t n, int64_t stride_n,
+                               int64_t stride_k, int mode, int mem, int32_t R, int segment_log2,
+                               uint8_t* out, size_t out_cap, size_t* out_len) {
+    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
+    if (!out_len) return fail(FLASHGMM_EINVAL, "null out_len");
+    int rc = check_gmm_args(scales, means, weights, n, stride_n, stride_k, mode, mem);
+    if (rc) return rc;
+    if (n > 0 && !symbols) return fail(FLASHGMM_EINVAL, "null symbols");
+    const int sl = il_seg_log2(segment_log2);
+    if (sl < 10 || sl > 16) return fail(FLASHGMM_EINVAL, "segment_log2 must be 0 (default) or in [10, 16]");
+    if (R < 0 || R > (1 << 22)) return fail(FLASHGMM_EINVAL, "R outside [0, 2^22]");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CU_TRY(cudaSetDevice(ctx->device));
+    Lane& L = lane_of(ctx, 0);
+    if ((rc = L.init())) return rc;
+    Slot& S = L.slot[0];
+    const int64_t n_seg = (n + ((int64_t)1 << sl) - 1) >> sl;
+    const int64_t cap = gmm_ileave_scratch_words(sl);
+    const size_t max_bytes = flashgmm_gmm_ileave_max_bytes(n, sl);
+    CU_TRY(ctx->il_scratch.need((size_t)std::max<int64_t>(1, n_seg) * cap * 2));
+    CU_TRY(ctx->il_segw.need((size_t)(n_seg + 1) * 4));
+    CU_TRY(ctx->il_out.need(max_bytes + 64));
+    CU_TRY(ctx->il_err.need(64));
+    CU_TRY(ctx->il_host.need(64));
+
+    flashgmm_stream s{};
+    s.symbols = symbols; s.scales = scales; s.means = means; s.weights = weights;
+    s.n = n; s.stride_n = stride_n; s.stride_k = stride_k;
+    GmmParamsView view{scales, means, weights, stride_n, stride_k};
+    const int32_t* sym_d = symbols;
+    if (mem == FLASHGMM_MEM_HOST && n > 0) {
+        if ((rc = stage_chunk(S, s, 0, n, true, &view, &sym_d))) return rc;
+    }
+    unsigned long long* d_total = static_cast<unsigned long long*>(ctx->il_err.p);
+    prof_begin(S, PROF_IL_ENC, 52.0 * (double)n);
+    CU_TRY(launch_gmm_ileave_encode(sym_d, view, n, mode, R, sl, static_cast<uint16_t*>(ctx->il_scratch.p),
+                                    static_cast<uint32_t*>(ctx->il_segw.p), static_cast<uint8_t*>(ctx->il_out.p),
+                                    d_total, S.st));
+    prof_end(S);
+    g_launches.fetch_add(n_seg > 0 ? 3 : 1, std::memory_order_relaxed);
+    CU_TRY(cudaMemcpyAsync(ctx->il_host.p, d_total, 8, cudaMemcpyDeviceToHost, S.st));
+    CU_TRY(cudaStreamSynchronize(S.st));
+    prof_collect(S);
+    const size_t total = (size_t)*static_cast<unsigned long long*>(ctx->il_host.p);
+    *out_len = total;
+    if (total > out_cap) return fail(FLASHGMM_ENOSPC, "output buffer too small: need %zu bytes, have %zu", total, out_cap);
+    if (!out) return fail(FLASHGMM_EINVAL, "null output buffer");
+    CU_TRY(cudaMemcpyAsync(out, ctx->il_out.p, total, cudaMemcpyDeviceToHost, S.st));
+    CU_TRY(cudaStreamSynchronize(S.st));
+    return FLASHGMM_OK;
+}
+
+int flashgmm_gmm_ileave_decode(flashgmm_ctx* ctx, const uint8_t* encoded, size_t encoded_len,
+                               const float* scales, const float* means, const float* weights, int64_t n,
+                               int64_t stride_n, int64_t stride_k, int mem, int32_t* symbols_out) {
+    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
+    int64_t hn; int mode, sl; int32_t R;
+    int rc = flashgmm_gmm_ileave_info(encoded, encoded_len, &hn, &mode, &R, &sl);
+    if (rc) return rc;
+    if (hn != n) return fail(FLASHGMM_EINVAL, "container holds %lld symbols, caller expects %lld", (long long)hn, (long long)n);
+    if ((rc = check_gmm_args(scales, means, weights, n, stride_n, stride_k, mode, mem))) return rc;
+    if (n > 0 && !symbols_out) return fail(FLASHGMM_EINVAL, "null symbols_out");
+    if (n == 0) return FLASHGMM_OK;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CU_TRY(cudaSetDevice(ctx->device));
+    Lane& L = lane_of(ctx, 0);
+    if ((rc = L.init())) return rc;
+    Slot& S = L.slot[0];
+    const uint32_t n_seg = (uint32_t)((n + ((int64_t)1 << sl) - 1) >> sl);
+    uint64_t pay; memcpy(&pay, encoded + 24, 8);
+    const size_t used = 32 + 4 * ((size_t)n_seg + 1) + (size_t)pay;
+    // host-side validation of the offset table (the kernel bounds-checks word reads inside a segment)
+    {
+        const uint8_t* ot = encoded + 32;
+        uint32_t prev = 0;
+        for (uint32_t k = 0; k <= n_seg; ++k) {
+            uint32_t o; memcpy(&o, ot + 4 * (size_t)k, 4);
+            if ((o & 3u) || o < prev || o > pay || (k == 0 && o != 0))
+                return fail(FLASHGMM_EINVAL, "corrupt FGIL offset table at segment %u", k);
+            prev = o;
+        }
+        if (prev != pay) return fail(FLASHGMM_EINVAL, "corrupt FGIL offset table (total)");
+    }
+    CU_TRY(ctx->il_out.need(used + 64));
+    CU_TRY(ctx->il_err.need(64));
+    CU_TRY(ctx->il_host.need(64));
+    CU_TRY(cudaMemcpyAsync(ctx->il_out.p, encoded, used, cudaMemcpyHostToDevice, S.st));
+    CU_TRY(cudaMemsetAsync(ctx->il_err.p, 0, 16, S.st));
+    flashgmm_stream s{};
+    s.scales = scales; s.means = means; s.weights = weights; s.n = n; s.stride_n = stride_n; s.stride_k = stride_k;
+    GmmParamsView view{scales, means, weights, stride_n, stride_k};
+    int32_t* out_d = symbols_out;
+    if (mem == FLASHGMM_MEM_HOST) {
+        const int32_t* unused;
+        if ((rc = stage_chunk(S, s, 0, n, false, &view, &unused))) return rc;
+        CU_TRY(S.d_out.need((size_t)n * 4));
+        out_d = static_cast<int32_t*>(S.d_out.p);
+    }
+    uint32_t* d_err = static_cast<uint32_t*>(ctx->il_err.p) + 2;
+    prof_begin(S, PROF_IL_DEC, 52.0 * (double)n);
+    CU_TRY(launch_gmm_ileave_decode(static_cast<const uint8_t*>(ctx->il_out.p), view, n, mode, R, sl, n_seg, out_d,
+                                    d_err, S.st));
+    prof_end(S);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU_TRY(cudaMemcpyAsync(ctx->il_host.p, d_err, 4, cudaMemcpyDeviceToHost, S.st));
+    if (mem == FLASHGMM_MEM_HOST)
+        CU_TRY(cudaMemcpyAsync(symbols_out, out_d, (size_t)n * 4, cudaMemcpyDeviceToHost, S.st));
+    CU_TRY(cudaStreamSynchronize(S.st));
+    prof_collect(S);
+    if (*static_cast<uint32_t*>(ctx->il_host.p) != 0)
+        return fail(FLASHGMM_ETRUNC, "interleaved stream is truncated or corrupt (segment reads ran past their end)");
+    return FLASHGMM_OK;
 }
 
 // ---- likelihood ----

@@ -31,6 +31,15 @@ int gmm_table_lut_offset(int R);
 cudaError_t launch_gmm_cdf_table(const GmmParamsView& p, int64_t n, int mode, int R, uint16_t* table,
                                  int row_stride, bool with_lut, cudaStream_t st);
 
+// Interleaved multi-lane rANS (gmm_ileave.cu). scratch: n_seg * gmm_ileave_scratch_words()
+// uint16; seg_words: n_seg uint32; out: device buffer for the whole container.
+int64_t gmm_ileave_scratch_words(int seg_log2);
+cudaError_t launch_gmm_ileave_encode(const int32_t* sym, const GmmParamsView& p, int64_t n, int mode, int R,
+                                     int seg_log2, uint16_t* scratch, uint32_t* seg_words, uint8_t* out,
+                                     unsigned long long* total_bytes, cudaStream_t st);
+cudaError_t launch_gmm_ileave_decode(const uint8_t* enc, const GmmParamsView& p, int64_t n, int mode, int R,
+                                     int seg_log2, uint32_t n_seg, int32_t* out, uint32_t* err, cudaStream_t st);
+
 // GaussianMixtureConditional likelihood (gmm_likelihood.cu). x / y / lik / grad are
 // (B, plane) contiguous; parameters are (B, K, plane) contiguous (plane = M*H*W).
 // quant: 0 = y = x, 1 = y = x + noise, 2 = y = rint(x).

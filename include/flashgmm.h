@@ -123,6 +123,25 @@ int flashgmm_gmm_encode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
 int flashgmm_gmm_decode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode,
                               int mem);
 
+/* ---- opt-in interleaved multi-lane rANS (own container format, GPU encodes AND decodes) ----
+ * No reference counterpart (the reference's single 64-bit state, rans64.h, is serial). Same
+ * per-symbol model as the compatible path -- the quantised CDF of RI:498-517 -- coded with
+ * 32 independent 32-bit rANS states per segment of 2^segment_log2 symbols (10..16;
+ * 0 = default 13). Symbols outside [-R, R] or with pmf == 0 are escaped (raw int32).
+ * Format: flashgmm_b200/csrc/gmm_ileave.cu. Bitstreams are host memory. */
+size_t flashgmm_gmm_ileave_max_bytes(int64_t n, int segment_log2);
+int flashgmm_gmm_ileave_encode(flashgmm_ctx* ctx, const int32_t* symbols, const float* scales,
+                               const float* means, const float* weights, int64_t n, int64_t stride_n,
+                               int64_t stride_k, int mode, int mem, int32_t R, int segment_log2,
+                               uint8_t* out, size_t out_cap, size_t* out_len);
+/* Reads n / mode / R / segment size from the container header (NULL outputs are skipped). */
+int flashgmm_gmm_ileave_info(const uint8_t* encoded, size_t encoded_len, int64_t* n, int* mode,
+                             int32_t* R, int* segment_log2);
+/* n must equal the header's; the APPROX_MODE used is the header's. */
+int flashgmm_gmm_ileave_decode(flashgmm_ctx* ctx, const uint8_t* encoded, size_t encoded_len,
+                               const float* scales, const float* means, const float* weights, int64_t n,
+                               int64_t stride_n, int64_t stride_k, int mem, int32_t* symbols_out);
+
 /* ---- training / evaluation likelihood (device pointers, asynchronous on `stream`) ---- */
 
 /* GaussianMixtureConditional.forward, EM:792-808 (+ _likelihood EM:774-790, 720-737,
@@ -178,7 +197,8 @@ uint64_t flashgmm_launch_count(void);
 /* Optional live kernel timing for roofline reports: when enabled, every kernel the
  * whole-call entry points launch is bracketed by CUDA events on its own stream.
  * kind 0 = gmm_startfreq (algorithmic bytes 56/symbol), 1 = gmm_cdf_table
- * (48 + 2*row_stride bytes/symbol). */
+ * (48 + 2*row_stride bytes/symbol), 2 = interleaved encode (52 B/symbol + stream),
+ * 3 = interleaved decode (48 B/symbol + stream + 4). */
 void flashgmm_profile_enable(int on);
 void flashgmm_profile_reset(void);
 int flashgmm_profile_read(int kind, double* total_ms, uint64_t* launches, double* algorithmic_bytes);

@@ -155,3 +155,34 @@ def gmm_likelihood_f64(x, scales, means, weights, K=4, scale_bound=0.11, lik_bou
     lib().fgo_gmm_likelihood_f64(_p(x), _p(sc), _p(mu), _p(w), C.c_int64(x.shape[0]), C.c_int64(sn),
                                  C.c_int64(sk), C.c_int(K), C.c_double(scale_bound), C.c_double(lik_bound), _p(out))
     return out
+
+
+def ileave_encode(symbols, scales, means, weights, R: int, mode=0, segment_log2=13) -> bytes:
+    """CPU statement of the interleaved container (flashgmm_b200/csrc/gmm_ileave.cu)."""
+    (sc, mu, w), sn, sk = _params(scales, means, weights)
+    sym = np.ascontiguousarray(symbols, np.int32)
+    n = sym.shape[0]
+    S = 1 << segment_log2
+    n_seg = (n + S - 1) >> segment_log2
+    cap = 32 + 4 * (n_seg + 1) + n_seg * 2 * (3 * S + 80)
+    out = np.empty(cap, np.uint8)
+    L = lib()
+    L.fgo_ileave_encode.restype = C.c_int64
+    nb = L.fgo_ileave_encode(_p(sym), _p(sc), _p(mu), _p(w), C.c_int64(n), C.c_int64(sn), C.c_int64(sk), C.c_int(mode),
+                             C.c_int32(R), C.c_int(segment_log2), _p(out), C.c_size_t(cap))
+    assert nb >= 0
+    return out[:nb].tobytes()
+
+
+def ileave_decode(encoded: bytes, scales, means, weights):
+    (sc, mu, w), sn, sk = _params(scales, means, weights)
+    n = sc.shape[0]
+    enc = np.frombuffer(encoded, np.uint8)
+    out = np.zeros(n, np.int32)
+    L = lib()
+    L.fgo_ileave_decode.restype = C.c_int
+    rc = L.fgo_ileave_decode(_p(enc), C.c_size_t(enc.size), _p(sc), _p(mu), _p(w), C.c_int64(n), C.c_int64(sn),
+                             C.c_int64(sk), _p(out))
+    if rc:
+        raise ValueError("malformed interleaved stream")
+    return out
