@@ -60,6 +60,15 @@ _SIGS = {
     "flashgmm_rans_pop_table": (C.c_int, [_vp, _sz, _vp, _i64, _i64, _i32, _vp]),
     "flashgmm_rans_encode_table": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _sz, C.POINTER(_sz)]),
     "flashgmm_rans_decode_table": (C.c_int, [_vp, _sz, _vp, _i64, _vp, _i64, _i64, _vp, _vp, _vp]),
+    "flashgmm_benc_create": (C.c_int, [C.POINTER(_vp)]),
+    "flashgmm_benc_destroy": (None, [_vp]),
+    "flashgmm_benc_entries": (_i64, [_vp]),
+    "flashgmm_benc_push_table": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _i64, _i64, _vp, _vp]),
+    "flashgmm_benc_push_gmm_packed": (C.c_int, [_vp, _vp, _vp, _i64]),
+    "flashgmm_benc_flush": (C.c_int, [_vp, _vp, _sz, C.POINTER(_sz)]),
+    "flashgmm_sdec_create": (C.c_int, [_vp, _sz, C.POINTER(_vp)]),
+    "flashgmm_sdec_destroy": (None, [_vp]),
+    "flashgmm_sdec_decode_table": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _i64, _vp, _vp, _vp]),
 }
 
 _lib = None

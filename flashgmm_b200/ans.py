@@ -209,3 +209,105 @@ class RansDecoder:
 
     def decode_with_indexes_gmm(self, encoded, scales, means, weights, max_bs_value):
         return gmm_decode(encoded, scales, means, weights, max_bs_value)
+
+
+def _gmm_packed_host(symbols, scales, means, weights, mode=None):
+    """(start | freq << 16) records of the startfreq kernel as host arrays (+ host symbols)."""
+    sym = _tensor(symbols, torch.int32)
+    (sc, mu, w), N, (sn, sk), dev = _gmm_views(scales, means, weights, sym.numel())
+    if dev.type == "cpu":      # buffered API with CPU tensors: run the kernel on the current device
+        cdev = torch.device("cuda", torch.cuda.current_device())
+        sym_d = sym.to(cdev)
+        sc, mu, w = (torch.stack([t[:, k] for k in range(4)]).to(cdev).t() for t in (sc, mu, w))
+        sn, sk = sc.stride()
+        dev = cdev
+    else:
+        if sym.device != dev:
+            raise ValueError("symbols and parameters must be on one device")
+        sym_d = sym
+    sym_d = sym_d.contiguous()
+    out = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream(dev)
+    mode = get_approx_mode() if mode is None else mode
+    _lib.check(_lib.lib().flashgmm_gmm_startfreq(_lib.ctx(_dev_index(dev)), sym_d.data_ptr(), sc.data_ptr(),
+                                                 mu.data_ptr(), w.data_ptr(), N, sn, sk, mode, out.data_ptr(),
+                                                 st.cuda_stream))
+    packed = out[:N].cpu().numpy().view(np.uint32)
+    return packed, sym.cpu().numpy()
+
+
+class BufferedRansEncoder:
+    """rans_interface.cpp:977-984 (+ :334-399, 458-585): several encode calls, one stream."""
+
+    def __init__(self):
+        h = C.c_void_p()
+        _lib.check(_lib.lib().flashgmm_benc_create(C.byref(h)))
+        self._h = h
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                _lib.lib().flashgmm_benc_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def encode_with_indexes(self, symbols, indexes, cdfs, cdfs_sizes, offsets) -> None:
+        sym = np.ascontiguousarray(symbols, np.int32)
+        idx = np.ascontiguousarray(indexes, np.int32)
+        if sym.shape != idx.shape or sym.ndim != 1:
+            raise ValueError("symbols / indexes must be 1-D and the same length")
+        m, sizes, offs = _cdf_matrix(cdfs, cdfs_sizes, offsets)
+        _lib.check(_lib.lib().flashgmm_benc_push_table(self._h, sym.ctypes.data, idx.ctypes.data, sym.size,
+                                                       m.ctypes.data, m.shape[0], m.shape[1], sizes.ctypes.data,
+                                                       offs.ctypes.data))
+
+    def encode_with_indexes_gmm(self, symbols, scales, means, weights, max_value=0) -> None:
+        packed, sym = _gmm_packed_host(symbols, scales, means, weights)
+        sym = np.ascontiguousarray(sym, np.int32)
+        _lib.check(_lib.lib().flashgmm_benc_push_gmm_packed(self._h, packed.ctypes.data, sym.ctypes.data, packed.size))
+
+    def flush(self) -> bytes:
+        L = _lib.lib()
+        cap = max(64, int(L.flashgmm_benc_entries(self._h)) * 4 + 64)
+        out = np.empty(cap, np.uint8)
+        n_out = C.c_size_t(0)
+        _lib.check(L.flashgmm_benc_flush(self._h, out.ctypes.data, cap, C.byref(n_out)))
+        return out[: n_out.value].tobytes()
+
+
+def _set_stream(self, encoded) -> None:
+    """RansDecoder.set_stream, rans_interface.cpp:886-893."""
+    buf = np.frombuffer(encoded, np.uint8)
+    if getattr(self, "_sdec", None):
+        _lib.lib().flashgmm_sdec_destroy(self._sdec)
+        self._sdec = None
+    h = C.c_void_p()
+    _lib.check(_lib.lib().flashgmm_sdec_create(buf.ctypes.data, buf.size, C.byref(h)))
+    self._sdec = h
+
+
+def _decode_stream(self, indexes, cdfs, cdfs_sizes, offsets):
+    """RansDecoder.decode_stream, rans_interface.cpp:895-956: continues where the last call stopped."""
+    if not getattr(self, "_sdec", None):
+        raise RuntimeError("decode_stream called before set_stream")
+    idx = np.ascontiguousarray(indexes, np.int32)
+    m, sizes, offs = _cdf_matrix(cdfs, cdfs_sizes, offsets)
+    out = np.empty(idx.size, np.int32)
+    _lib.check(_lib.lib().flashgmm_sdec_decode_table(self._sdec, idx.ctypes.data, idx.size, m.ctypes.data, m.shape[0],
+                                                     m.shape[1], sizes.ctypes.data, offs.ctypes.data, out.ctypes.data))
+    return out.tolist()
+
+
+def _dec_del(self):
+    try:
+        if getattr(self, "_sdec", None):
+            _lib.lib().flashgmm_sdec_destroy(self._sdec)
+            self._sdec = None
+    except Exception:
+        pass
+
+
+RansDecoder.set_stream = _set_stream
+RansDecoder.decode_stream = _decode_stream
+RansDecoder.__del__ = _dec_del

@@ -922,14 +922,9 @@ int flashgmm_rans_encode_table(const int32_t* symbols, const int32_t* indexes, i
     return emit(bb, out, out_cap, out_len);
 }
 
-int flashgmm_rans_decode_table(const uint8_t* encoded, size_t encoded_len, const int32_t* indexes,
-                               int64_t n, const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
-                               const int32_t* cdf_sizes, const int32_t* offsets, int32_t* symbols_out) {
-    if (!encoded || (n > 0 && !symbols_out)) return fail(FLASHGMM_EINVAL, "bad argument");
-    int rc = check_table_args(indexes, n, cdfs, n_cdfs, cdf_stride, cdf_sizes, offsets);
-    if (rc) return rc;
-    RansDecoder64 dec;
-    dec.init(encoded, encoded_len);
+static void decode_table_run(RansDecoder64& dec, const int32_t* indexes, int64_t n, const int32_t* cdfs,
+                             int64_t cdf_stride, const int32_t* cdf_sizes, const int32_t* offsets,
+                             int32_t* symbols_out) {
     for (int64_t i = 0; i < n; ++i) {
         const int32_t ci = indexes[i];
         const int32_t* cdf = cdfs + (int64_t)ci * cdf_stride;
@@ -951,7 +946,121 @@ int flashgmm_rans_decode_table(const uint8_t* encoded, size_t encoded_len, const
         }
         symbols_out[i] = value + offsets[ci];
     }
+}
+
+int flashgmm_rans_decode_table(const uint8_t* encoded, size_t encoded_len, const int32_t* indexes,
+                               int64_t n, const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
+                               const int32_t* cdf_sizes, const int32_t* offsets, int32_t* symbols_out) {
+    if (!encoded || (n > 0 && !symbols_out)) return fail(FLASHGMM_EINVAL, "bad argument");
+    int rc = check_table_args(indexes, n, cdfs, n_cdfs, cdf_stride, cdf_sizes, offsets);
+    if (rc) return rc;
+    RansDecoder64 dec;
+    dec.init(encoded, encoded_len);
+    decode_table_run(dec, indexes, n, cdfs, cdf_stride, cdf_sizes, offsets, symbols_out);
     if (dec.overrun) return fail(FLASHGMM_ETRUNC, "bitstream truncated");
+    return FLASHGMM_OK;
+}
+
+// ---- sessions ----
+struct flashgmm_buffered_encoder {
+    struct Sym { uint16_t start, range; uint8_t bypass; };     // rans_interface.hpp:48-52
+    std::vector<Sym> syms;
+    inline void raw_nibbles(uint32_t raw) {                     // count prefix + nibbles, RI:372-397 / 524-552
+        int32_t nb = 0;
+        while (nb < 8 && (raw >> (nb * 4)) != 0) ++nb;
+        int32_t v = nb;
+        while (v >= (int32_t)kBypassMax) { syms.push_back({(uint16_t)kBypassMax, (uint16_t)(kBypassMax + 1), 1}); v -= kBypassMax; }
+        syms.push_back({(uint16_t)v, (uint16_t)(v + 1), 1});
+        for (int32_t j = 0; j < nb; ++j) {
+            uint16_t q = (uint16_t)((raw >> (j * 4)) & kBypassMax);
+            syms.push_back({q, (uint16_t)(q + 1), 1});
+        }
+    }
+};
+
+int flashgmm_benc_create(flashgmm_buffered_encoder** out) {
+    if (!out) return fail(FLASHGMM_EINVAL, "null out pointer");
+    *out = new flashgmm_buffered_encoder();
+    rcp_table();
+    return FLASHGMM_OK;
+}
+void flashgmm_benc_destroy(flashgmm_buffered_encoder* enc) { delete enc; }
+int64_t flashgmm_benc_entries(const flashgmm_buffered_encoder* enc) { return enc ? (int64_t)enc->syms.size() : -1; }
+
+int flashgmm_benc_push_table(flashgmm_buffered_encoder* enc, const int32_t* symbols, const int32_t* indexes,
+                             int64_t n, const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
+                             const int32_t* cdf_sizes, const int32_t* offsets) {
+    if (!enc || (n > 0 && !symbols)) return fail(FLASHGMM_EINVAL, "bad argument");
+    int rc = check_table_args(indexes, n, cdfs, n_cdfs, cdf_stride, cdf_sizes, offsets);
+    if (rc) return rc;
+    for (int64_t i = 0; i < n; ++i) {
+        const int32_t ci = indexes[i];
+        const int32_t* cdf = cdfs + (int64_t)ci * cdf_stride;
+        const int32_t max_value = cdf_sizes[ci] - 2;
+        int32_t value = symbols[i] - offsets[ci];
+        uint32_t raw = 0;
+        if (value < 0) { raw = (uint32_t)(-2 * value - 1); value = max_value; }
+        else if (value >= max_value) { raw = (uint32_t)(2 * (value - max_value)); value = max_value; }
+        const uint16_t range = (uint16_t)(cdf[value + 1] - cdf[value]);
+        if (range == 0) return fail(FLASHGMM_EINVAL, "zero-frequency symbol at %lld (invalid CDF)", (long long)i);
+        enc->syms.push_back({(uint16_t)cdf[value], range, 0});
+        if (value == max_value) enc->raw_nibbles(raw);
+    }
+    return FLASHGMM_OK;
+}
+
+int flashgmm_benc_push_gmm_packed(flashgmm_buffered_encoder* enc, const uint32_t* packed,
+                                  const int32_t* symbols, int64_t n) {
+    if (!enc || n < 0 || (n > 0 && !packed)) return fail(FLASHGMM_EINVAL, "bad argument");
+    for (int64_t i = 0; i < n; ++i) {
+        const uint32_t pk = packed[i], freq = pk >> 16;
+        if (freq) { enc->syms.push_back({(uint16_t)(pk & 0xffffu), (uint16_t)freq, 0}); continue; }
+        if (!symbols) return fail(FLASHGMM_EINVAL, "bypass record at %lld needs symbols", (long long)i);
+        enc->syms.push_back({(uint16_t)kMaxCdf, 1, 0});        // RI:513-521
+        enc->raw_nibbles((uint32_t)symbols[i]);
+    }
+    return FLASHGMM_OK;
+}
+
+int flashgmm_benc_flush(flashgmm_buffered_encoder* enc, uint8_t* out, size_t out_cap, size_t* out_len) {
+    if (!enc || !out_len || (!out && out_cap)) return fail(FLASHGMM_EINVAL, "bad argument");
+    BackBuffer bb(enc->syms.size() / 2 + 64);
+    RansEncoder64 r;
+    r.init(&bb);
+    for (size_t k = enc->syms.size(); k-- > 0;) {              // reverse walk, RI:569-577
+        if ((k & 1023) == 1023 || k + 1 == enc->syms.size()) bb.reserve(1024 + 8);
+        const auto& s = enc->syms[k];
+        if (s.bypass) r.put_bits4(s.start); else r.put(s.start, s.range);
+    }
+    r.flush();
+    int rc = emit(bb, out, out_cap, out_len);
+    if (rc == FLASHGMM_OK) enc->syms.clear();                  // on ENOSPC the caller retries with a larger buffer
+    return rc;
+}
+
+struct flashgmm_stream_decoder {
+    std::vector<uint8_t> stream;
+    RansDecoder64 dec;
+};
+
+int flashgmm_sdec_create(const uint8_t* encoded, size_t encoded_len, flashgmm_stream_decoder** out) {
+    if (!out || !encoded) return fail(FLASHGMM_EINVAL, "bad argument");
+    auto* d = new flashgmm_stream_decoder();
+    d->stream.assign(encoded, encoded + encoded_len);          // set_stream copies, RI:887
+    d->dec.init(d->stream.data(), d->stream.size());
+    *out = d;
+    return FLASHGMM_OK;
+}
+void flashgmm_sdec_destroy(flashgmm_stream_decoder* dec) { delete dec; }
+
+int flashgmm_sdec_decode_table(flashgmm_stream_decoder* dec, const int32_t* indexes, int64_t n,
+                               const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
+                               const int32_t* cdf_sizes, const int32_t* offsets, int32_t* symbols_out) {
+    if (!dec || (n > 0 && !symbols_out)) return fail(FLASHGMM_EINVAL, "bad argument");
+    int rc = check_table_args(indexes, n, cdfs, n_cdfs, cdf_stride, cdf_sizes, offsets);
+    if (rc) return rc;
+    decode_table_run(dec->dec, indexes, n, cdfs, cdf_stride, cdf_sizes, offsets, symbols_out);
+    if (dec->dec.overrun) return fail(FLASHGMM_ETRUNC, "bitstream truncated");
     return FLASHGMM_OK;
 }
 

@@ -191,6 +191,32 @@ int flashgmm_rans_decode_table(const uint8_t* encoded, size_t encoded_len, const
                                int64_t n, const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
                                const int32_t* cdf_sizes, const int32_t* offsets, int32_t* symbols_out);
 
+/* ---- buffered encoder / streaming decoder sessions (host state objects) ----
+ * BufferedRansEncoder (RI:334-399, 458-585, 977-984): symbols of several calls accumulate
+ * into one stream produced by flush(). */
+typedef struct flashgmm_buffered_encoder flashgmm_buffered_encoder;
+int flashgmm_benc_create(flashgmm_buffered_encoder** out);
+void flashgmm_benc_destroy(flashgmm_buffered_encoder* enc);
+/* BufferedRansEncoder::encode_with_indexes(symbols, indexes, cdfs, cdfs_sizes, offsets), RI:334-399 */
+int flashgmm_benc_push_table(flashgmm_buffered_encoder* enc, const int32_t* symbols, const int32_t* indexes,
+                             int64_t n, const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
+                             const int32_t* cdf_sizes, const int32_t* offsets);
+/* BufferedRansEncoder::encode_with_indexes_gmm, RI:458-554, fed with the packed records of
+ * flashgmm_gmm_startfreq (host copies); symbols are needed for bypass records only. */
+int flashgmm_benc_push_gmm_packed(flashgmm_buffered_encoder* enc, const uint32_t* packed,
+                                  const int32_t* symbols, int64_t n);
+/* BufferedRansEncoder::flush, RI:557-585: emits the stream and clears the session. */
+int flashgmm_benc_flush(flashgmm_buffered_encoder* enc, uint8_t* out, size_t out_cap, size_t* out_len);
+int64_t flashgmm_benc_entries(const flashgmm_buffered_encoder* enc);
+
+/* RansDecoder::set_stream / decode_stream, RI:886-956: the state persists between calls. */
+typedef struct flashgmm_stream_decoder flashgmm_stream_decoder;
+int flashgmm_sdec_create(const uint8_t* encoded, size_t encoded_len, flashgmm_stream_decoder** out);
+void flashgmm_sdec_destroy(flashgmm_stream_decoder* dec);
+int flashgmm_sdec_decode_table(flashgmm_stream_decoder* dec, const int32_t* indexes, int64_t n,
+                               const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
+                               const int32_t* cdf_sizes, const int32_t* offsets, int32_t* symbols_out);
+
 /* Kernel launches issued by this process through the library (bench.py's gpu_launches). */
 uint64_t flashgmm_launch_count(void);
 

@@ -66,6 +66,27 @@ def main():
                                         [list(map(int, r)) for r in kw["cdfs"]],
                                         list(map(int, kw["cdf_sizes"])), list(map(int, kw["offsets"])))
             return np.asarray(o, np.int32)
+        if op == "buffered":      # BufferedRansEncoder: a list of ("table", ...) / ("gmm", ...) pushes, one flush
+            be = ans.BufferedRansEncoder()
+            for kind, a in kw["pushes"]:
+                if kind == "table":
+                    be.encode_with_indexes(list(map(int, a["symbols"])), list(map(int, a["indexes"])),
+                                           [list(map(int, r)) for r in a["cdfs"]], list(map(int, a["cdf_sizes"])),
+                                           list(map(int, a["offsets"])))
+                else:
+                    sc, mu, w = params(a)
+                    be.encode_with_indexes_gmm(torch.from_numpy(np.ascontiguousarray(a["symbols"], np.int32)), sc, mu, w,
+                                               int(a.get("max_value", 0)))
+            return bytes(be.flush())
+        if op == "decode_stream":  # set_stream once, then one decode_stream call per index list
+            d2 = ans.RansDecoder()
+            d2.set_stream(kw["encoded"])
+            outs = []
+            for idx in kw["index_lists"]:
+                outs.append(np.asarray(d2.decode_stream(list(map(int, idx)), [list(map(int, r)) for r in kw["cdfs"]],
+                                                        list(map(int, kw["cdf_sizes"])), list(map(int, kw["offsets"]))),
+                                       np.int32))
+            return outs
         if op == "put":           # keep a stream resident in the worker (bench: no pickling inside a step)
             store[kw["key"]] = (torch.from_numpy(np.ascontiguousarray(kw["symbols"], np.int32)), params(kw),
                                 int(kw["max_bs_value"]))

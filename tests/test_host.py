@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 from flashgmm_b200 import _lib, ans, synth
-from oracle import port
+from oracle import port, ref
 from helpers import make_rows, row_stride
 
 ROOT = Path(__file__).resolve().parents[1]
@@ -192,6 +192,66 @@ def test_table_coder_matches_oracle():
     assert np.array_equal(ans.table_decode(want, idx, cdfs, sizes, offsets), sym)
     assert ans.RansDecoder().decode_with_indexes(want, idx.tolist(), cdfs.tolist(), sizes.tolist(), offsets.tolist()) == sym.tolist()
     assert ans.table_encode([], [], cdfs, sizes, offsets) == port.table_encode(sym[:0], idx[:0], cdfs, sizes, offsets)
+
+
+def _toy_cdfs(r, n_cdfs=5, width=64):
+    cdfs = np.zeros((n_cdfs, width), np.int32)
+    sizes = np.zeros(n_cdfs, np.int32)
+    for c in range(n_cdfs):
+        m = int(r.integers(3, width - 2))
+        q = np.maximum(1, np.floor(r.dirichlet(np.ones(m + 1)) * 65000)).astype(np.int64)
+        q[np.argmax(q)] += 65536 - q.sum()
+        cdfs[c, 1:m + 2] = np.cumsum(q)
+        sizes[c] = m + 2
+    return cdfs, sizes, -(sizes // 2).astype(np.int32)
+
+
+def test_buffered_encoder_and_stream_decoder(ref_available):
+    """BufferedRansEncoder (rans_interface.cpp:334-399, 557-585) and set_stream / decode_stream
+    (:886-956): several pushes make ONE stream; the decoder's state persists across calls."""
+    r = np.random.default_rng(8)
+    cdfs, sizes, offsets = _toy_cdfs(r)
+    n = 6000
+    idx = r.integers(0, len(sizes), n).astype(np.int32)
+    sym = r.normal(0, 8, n).round().astype(np.int32)
+    sym[:3] = [2**20, -2**20, 0]
+    be = ans.BufferedRansEncoder()
+    be.encode_with_indexes(sym[:2500], idx[:2500], cdfs, sizes, offsets)
+    be.encode_with_indexes(sym[2500:].tolist(), idx[2500:].tolist(), cdfs.tolist(), sizes.tolist(), offsets.tolist())
+    b = be.flush()
+    assert b == port.table_encode(sym, idx, cdfs, sizes, offsets)          # == one-shot encode of the concatenation
+    assert be.flush() == port.table_encode(sym[:0], idx[:0], cdfs, sizes, offsets)   # session cleared: empty stream
+    d = ans.RansDecoder()
+    with pytest.raises(RuntimeError):
+        d.decode_stream(idx[:1], cdfs, sizes, offsets)
+    d.set_stream(b)
+    a1 = d.decode_stream(idx[:1000], cdfs, sizes, offsets)
+    a2 = d.decode_stream(idx[1000:].tolist(), cdfs.tolist(), sizes.tolist(), offsets.tolist())
+    assert a1 + a2 == sym.tolist()
+    # GMM records pushed through the session (packed words as the startfreq kernel emits them)
+    gs, sg, mu, w = synth.gmm_numpy(3000, seed=77, sigma_span=1.0)
+    gs = gs.copy(); gs[:2] = [400, -9]
+    st, fr, bp = port.gmm_startfreq(gs, sg, mu, w, 0)
+    packed = st.astype(np.uint32) | (fr.astype(np.uint32) << 16)
+    packed[bp == 1] = 0xFFFF
+    L = _lib.lib()
+    _lib.check(L.flashgmm_benc_push_gmm_packed(be._h, packed.ctypes.data, gs.ctypes.data, packed.size))
+    assert be.flush() == port.gmm_encode(gs, sg, mu, w, 0)
+    if ref_available:
+        rows = [cdfs[c, :sizes[c]] for c in range(len(sizes))]
+        with ref.RefWorker(0) as wk:
+            tab = dict(symbols=sym[:2500], indexes=idx[:2500], cdfs=rows, cdf_sizes=sizes, offsets=offsets)
+            tab2 = dict(symbols=sym[2500:], indexes=idx[2500:], cdfs=rows, cdf_sizes=sizes, offsets=offsets)
+            assert wk.call("buffered", pushes=[("table", tab), ("table", tab2)]) == b
+            outs = wk.call("decode_stream", encoded=b, index_lists=[idx[:1000], idx[1000:]], cdfs=rows, cdf_sizes=sizes,
+                           offsets=offsets)
+            assert np.concatenate(outs).tolist() == sym.tolist()
+            # mixed session: table symbols then GMM symbols in one stream
+            gm = dict(symbols=gs, scales=sg, means=mu, weights=w)
+            mixed_ref = wk.call("buffered", pushes=[("table", tab), ("gmm", gm)])
+        be.encode_with_indexes(sym[:2500], idx[:2500], cdfs, sizes, offsets)
+        _lib.check(L.flashgmm_benc_push_gmm_packed(be._h, packed.ctypes.data, gs.ctypes.data, packed.size))
+        assert be.flush() == mixed_ref
 
 
 def test_error_behaviour():

@@ -109,3 +109,20 @@ def test_table_coder_roundtrip_and_reference(ref_available):
             rows = [cdfs[c, :sizes[c]] for c in range(n_cdfs)]
             assert wk.table_encode(sym, idx, rows, sizes, offsets) == b
             assert np.array_equal(wk.table_decode(b, idx, rows, sizes, offsets), sym)
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_phi_is_monotone_on_sampled_windows(mode):
+    """Windows of consecutive floats (the exhaustive run over all 2^32 is oracle/check_monotone.c):
+    a monotone Phi makes every quantised CDF row non-decreasing, which the interleaved decoder's
+    bisection and the compatible decoder's fast path rely on."""
+    import ctypes as C
+    import struct
+
+    L = port.lib()
+    L.fgo_phi_count_decreasing.restype = C.c_int64
+    r = np.random.default_rng(3)
+    starts = [1e-30, 1e-6, 0.01, 0.4999, 1.0, 2.0, 3.3, 5.2, 5.9, 9.0, 13.2, 40.0] + list(10 ** r.uniform(-3, 1.5, 8))
+    for t0 in starts:
+        bits = struct.unpack("<I", struct.pack("<f", t0))[0]
+        assert L.fgo_phi_count_decreasing(C.c_int(mode), C.c_uint32(bits), C.c_uint32(400_000)) == 0, t0
