@@ -215,7 +215,7 @@ def run_b200(args):
     # per-kernel CUDA-event timing in a second pass (events add host work to every launch)
     timed(enc_d, dec_d, max(2, args.steps // 4), profile=True)
     prof = {}
-    for kind, name in ((0, "gmm_startfreq"), (1, "gmm_cdf_rows")):
+    for kind, name in ((0, "gmm_startfreq"), (1, "gmm_cdf_rows"), (4, "gmm_pop_rows")):
         ms, n, by = C.c_double(), C.c_uint64(), C.c_double()
         L.flashgmm_profile_read(kind, C.byref(ms), C.byref(n), C.byref(by))
         prof[name] = dict(ms=ms.value, launches=n.value, bytes=by.value)

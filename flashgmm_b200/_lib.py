@@ -72,7 +72,7 @@ _SIGS = {
 }
 
 _lib = None
-_lock = threading.Lock()
+_lock = threading.RLock()   # ctx() calls lib() while holding it
 _ctxs: dict = {}
 
 

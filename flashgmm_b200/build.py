@@ -27,6 +27,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-O3,-fno-strict
 UNITS = [
     ("gmm_kernels.cu", ["-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false"]),
     ("gmm_ileave.cu", ["-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false"]),
+    ("gmm_pop.cu", ["-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false", "-Xptxas", "-v"]),
     ("gmm_likelihood.cu", ["-Xptxas", "-v"]),
     ("flashgmm_abi.cu", ["-Xcompiler", "-march=x86-64-v3"]),
 ]

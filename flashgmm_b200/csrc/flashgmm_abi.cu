@@ -34,7 +34,7 @@ std::atomic<uint64_t> g_launches{0};
 
 // Optional per-kernel timing (bench.py's live roofline): CUDA events around each
 // launch on the launching stream, read back when the chunk is consumed.
-enum { PROF_STARTFREQ = 0, PROF_TABLE = 1, PROF_IL_ENC = 2, PROF_IL_DEC = 3, PROF_KINDS = 4 };
+enum { PROF_STARTFREQ = 0, PROF_TABLE = 1, PROF_IL_ENC = 2, PROF_IL_DEC = 3, PROF_POP = 4, PROF_KINDS = 5 };
 std::atomic<int> g_prof_on{0};
 std::mutex g_prof_mu;
 double g_prof_ms[PROF_KINDS] = {};
@@ -186,6 +186,53 @@ private:
     bool stop_ = false;
 };
 
+// Buffers, streams and events of the device-resident decode path.
+struct DevDecode {
+    cudaStream_t st_rows = nullptr, st_pop = nullptr, st_copy = nullptr;
+    std::vector<cudaEvent_t> ev_rows, ev_pop, ev_up;      // one per chunk (grown on demand)
+    std::vector<cudaEvent_t> t0, t1;                      // kernel timing pairs (profiling only)
+    cudaEvent_t ev_words = nullptr;
+    DevBuf rows[2], words, desc, state, params, out;
+    PinBuf h_desc, h_words, h_state;
+    int init() {
+        if (st_rows) return FLASHGMM_OK;
+        CU_TRY(cudaStreamCreateWithFlags(&st_rows, cudaStreamNonBlocking));
+        CU_TRY(cudaStreamCreateWithFlags(&st_pop, cudaStreamNonBlocking));
+        CU_TRY(cudaStreamCreateWithFlags(&st_copy, cudaStreamNonBlocking));
+        CU_TRY(cudaEventCreateWithFlags(&ev_words, cudaEventDisableTiming));
+        return FLASHGMM_OK;
+    }
+    int need_events(size_t n) {
+        while (ev_rows.size() < n) {
+            cudaEvent_t a, b, c;
+            CU_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+            CU_TRY(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+            CU_TRY(cudaEventCreateWithFlags(&c, cudaEventDisableTiming));
+            ev_rows.push_back(a); ev_pop.push_back(b); ev_up.push_back(c);
+        }
+        return FLASHGMM_OK;
+    }
+    int need_timers(size_t n) {
+        while (t0.size() < n) {
+            cudaEvent_t a, b;
+            CU_TRY(cudaEventCreate(&a));
+            CU_TRY(cudaEventCreate(&b));
+            t0.push_back(a); t1.push_back(b);
+        }
+        return FLASHGMM_OK;
+    }
+    void destroy() {
+        for (auto v : {&ev_rows, &ev_pop, &ev_up, &t0, &t1}) { for (auto e : *v) cudaEventDestroy(e); v->clear(); }
+        if (ev_words) cudaEventDestroy(ev_words);
+        if (st_rows) cudaStreamDestroy(st_rows);
+        if (st_pop) cudaStreamDestroy(st_pop);
+        if (st_copy) cudaStreamDestroy(st_copy);
+        st_rows = st_pop = st_copy = nullptr; ev_words = nullptr;
+        rows[0].release(); rows[1].release(); words.release(); desc.release(); state.release();
+        params.release(); out.release(); h_desc.release(); h_words.release(); h_state.release();
+    }
+};
+
 }  // namespace
 
 struct flashgmm_ctx {
@@ -199,6 +246,10 @@ struct flashgmm_ctx {
     // interleaved coder (whole-stream buffers, lane 0's first stream)
     DevBuf il_scratch, il_segw, il_out, il_err;
     PinBuf il_host;
+    // device-resident decode (rows kernel -> pop kernel, nothing but symbols leaves the GPU)
+    std::unique_ptr<DevDecode> dd;
+    int pop_min_streams = 4;          // batches at least this large decode on the device
+    int64_t pop_rows_budget = 512ll << 20;
 };
 
 namespace {
@@ -461,6 +512,273 @@ Lane& lane_of(flashgmm_ctx* ctx, int idx) {
     return *ctx->lanes[idx];
 }
 
+
+// ---------------- decode a batch of streams entirely on the device ----------------
+// rows kernel (all streams of a chunk in one launch) -> pop kernel (one warp per stream);
+// chunk c+1's rows are computed while chunk c is popped. Only bitstreams go up and decoded
+// symbols come down (mem == HOST additionally stages the parameters chunk by chunk).
+constexpr int32_t kMaxDevicePopR = kPopMaxR;   // 4 intervals per lane; wider searches stay on the host path
+
+int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem) {
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CU_TRY(cudaSetDevice(ctx->device));
+    if (!ctx->dd) ctx->dd.reset(new DevDecode());
+    DevDecode& D = *ctx->dd;
+    int rc = D.init();
+    if (rc) return rc;
+
+    // ---- validate, size ----
+    std::vector<int> act;                       // streams that take part
+    int worst = FLASHGMM_OK;
+    int64_t max_n = 0, total_n = 0;
+    size_t total_words = 0;
+    int32_t max_R = 0;
+    for (int i = 0; i < n_streams; ++i) {
+        flashgmm_stream& s = streams[i];
+        s.status = check_gmm_args(s.scales, s.means, s.weights, s.n, s.stride_n, s.stride_k, mode, mem);
+        if (!s.status && !s.bytes) s.status = fail(FLASHGMM_EINVAL, "null bitstream");
+        if (!s.status && s.n > 0 && !s.symbols_out) s.status = fail(FLASHGMM_EINVAL, "null symbols_out");
+        if (!s.status && (s.max_bs_value < 0 || s.max_bs_value > kMaxDevicePopR))
+            s.status = fail(FLASHGMM_EINVAL, "max_bs_value %d outside [0, %d]", s.max_bs_value, kMaxDevicePopR);
+        if (!s.status && s.n > INT32_MAX / 2) s.status = fail(FLASHGMM_EINVAL, "stream too long for one call");
+        if (s.status) { worst = s.status; continue; }
+        if (s.n == 0) continue;
+        act.push_back(i);
+        max_n = std::max(max_n, s.n);
+        total_n += s.n;
+        total_words += (s.bytes_cap / 4 + 3) / 4 * 4;       // 16-byte aligned slots
+        max_R = std::max(max_R, s.max_bs_value);
+    }
+    const int na = (int)act.size();
+    if (na == 0) return worst;
+
+    std::vector<int32_t> rs(na);
+    std::vector<size_t> word_off(na), out_off(na), par_off(na), npad(na);
+    {
+        size_t wo = 0, oo = 0, po = 0;
+        for (int a = 0; a < na; ++a) {
+            const flashgmm_stream& s = streams[act[a]];
+            rs[a] = gmm_table_lut_offset(s.max_bs_value);        // compact tile width (uint16) inside the rows kernel
+            word_off[a] = wo; wo += (s.bytes_cap / 4 + 3) / 4 * 4;
+            out_off[a] = oo; oo += (size_t)round_up(s.n, 4);
+            npad[a] = (size_t)round_up(s.n, 4);
+            par_off[a] = po; po += 12 * npad[a];
+        }
+    }
+    const int max_row_words = gmm_table_lut_offset(max_R) / 2;
+    const int lane_slots = gmm_pop_lane_slots(max_R);
+    const int64_t rec_bytes = 4 * (int64_t)lane_slots;             // lane-row record per symbol
+    int S = (int)std::min<int64_t>(32, (48 * 1024) / ((12 + max_row_words + 1) * 4));
+    if (total_n < 148 * 8 * 32) S = std::min(S, 8);
+
+    // ---- chunk boundaries (symbol offsets common to all streams) ----
+    auto chunk_bytes = [&](int64_t lo, int64_t hi) {
+        int64_t b = 0;
+        for (int a = 0; a < na; ++a) {
+            const int64_t n = streams[act[a]].n;
+            if (n > lo) b += (std::min(n, hi) - lo) * rec_bytes;
+        }
+        return b;
+    };
+    std::vector<int64_t> bound{0};
+    {
+        int64_t step = 4096;
+        while (bound.back() < max_n) {
+            const int64_t lo = bound.back();
+            int64_t st = step;
+            while (st > 256 && chunk_bytes(lo, lo + st) > ctx->pop_rows_budget) st /= 2;
+            bound.push_back(std::min(max_n, lo + st));
+            step = std::min<int64_t>(32768, step * 3);
+        }
+    }
+    const int nch = (int)bound.size() - 1;
+    if ((rc = D.need_events(nch))) return rc;
+    const bool prof = g_prof_on.load(std::memory_order_relaxed) != 0;
+    if (prof && (rc = D.need_timers(2 * (size_t)nch))) return rc;
+
+    // ---- device buffers ----
+    int64_t max_chunk_bytes = 0;
+    for (int c = 0; c < nch; ++c) max_chunk_bytes = std::max(max_chunk_bytes, chunk_bytes(bound[c], bound[c + 1]));
+    CU_TRY(D.rows[0].need((size_t)max_chunk_bytes));
+    if (nch > 1) CU_TRY(D.rows[1].need((size_t)max_chunk_bytes));
+    CU_TRY(D.words.need(total_words * 4 + 16));
+    CU_TRY(D.h_words.need(total_words * 4 + 16));
+    CU_TRY(D.state.need((size_t)na * 16));
+    CU_TRY(D.h_state.need((size_t)na * 16));
+    int32_t* d_out = nullptr;
+    float* d_par = nullptr;
+    if (mem == FLASHGMM_MEM_HOST) {
+        CU_TRY(D.out.need((out_off[na - 1] + npad[na - 1]) * 4));
+        CU_TRY(D.params.need((par_off[na - 1] + 12 * npad[na - 1]) * 4));
+        d_out = static_cast<int32_t*>(D.out.p);
+        d_par = static_cast<float*>(D.params.p);
+    }
+
+    // ---- descriptors for every chunk, one upload ----
+    struct ChunkInfo { int first, count, blocks; };
+    std::vector<ChunkInfo> ci(nch);
+    size_t n_desc = 0;
+    for (int c = 0; c < nch; ++c)
+        for (int a = 0; a < na; ++a) n_desc += streams[act[a]].n > bound[c] ? 1 : 0;
+    const size_t rows_desc_bytes = (n_desc * sizeof(RowsDesc) + 15) / 16 * 16;
+    CU_TRY(D.h_desc.need(rows_desc_bytes + n_desc * sizeof(PopDesc)));
+    CU_TRY(D.desc.need(rows_desc_bytes + n_desc * sizeof(PopDesc)));
+    RowsDesc* h_rd = static_cast<RowsDesc*>(D.h_desc.p);
+    PopDesc* h_pd = reinterpret_cast<PopDesc*>(static_cast<char*>(D.h_desc.p) + rows_desc_bytes);
+    RowsDesc* d_rd = static_cast<RowsDesc*>(D.desc.p);
+    PopDesc* d_pd = reinterpret_cast<PopDesc*>(static_cast<char*>(D.desc.p) + rows_desc_bytes);
+    auto stream_view = [&](int a, int64_t c0) -> GmmParamsView {
+        const flashgmm_stream& s = streams[act[a]];
+        if (mem == FLASHGMM_MEM_DEVICE) return device_view(s, c0);
+        float* b = d_par + par_off[a];
+        if (s.stride_n == 1)
+            return GmmParamsView{b + c0, b + 4 * npad[a] + c0, b + 8 * npad[a] + c0, 1, (int64_t)npad[a]};
+        return GmmParamsView{b + 4 * c0, b + 4 * npad[a] + 4 * c0, b + 8 * npad[a] + 4 * c0, 4, 1};
+    };
+    {
+        size_t k = 0;
+        for (int c = 0; c < nch; ++c) {
+            ci[c].first = (int)k;
+            int blocks = 0;
+            size_t roff = 0;
+            char* rbase = static_cast<char*>(D.rows[c & 1].p);
+            for (int a = 0; a < na; ++a) {
+                const flashgmm_stream& s = streams[act[a]];
+                if (s.n <= bound[c]) continue;
+                const int64_t c0 = bound[c], cnt = std::min(s.n, bound[c + 1]) - c0;
+                RowsDesc& r = h_rd[k];
+                r.p = stream_view(a, c0);
+                r.table32 = reinterpret_cast<uint32_t*>(rbase + roff);
+                r.n = (int32_t)cnt; r.R = s.max_bs_value; r.row_words = rs[a] / 2; r.first_block = blocks;
+                PopDesc& q = h_pd[k];
+                q.rows = reinterpret_cast<const uint16_t*>(rbase + roff);
+                q.words = static_cast<const uint32_t*>(D.words.p) + word_off[a];
+                q.out = (mem == FLASHGMM_MEM_DEVICE ? s.symbols_out : d_out + out_off[a]) + c0;
+                q.state = static_cast<uint64_t*>(D.state.p) + 2 * (size_t)a;
+                q.p = r.p;
+                q.n = (int32_t)cnt; q.R = s.max_bs_value;
+                q.n_words = (uint32_t)(s.bytes_cap / 4); q.first = c0 == 0 ? 1 : 0;
+                blocks += (int)((cnt + S - 1) / S);
+                roff += (size_t)cnt * rec_bytes;
+                ++k;
+            }
+            ci[c].count = (int)k - ci[c].first;
+            ci[c].blocks = blocks;
+        }
+    }
+    CU_TRY(cudaMemcpyAsync(D.desc.p, D.h_desc.p, rows_desc_bytes + n_desc * sizeof(PopDesc), cudaMemcpyHostToDevice,
+                           D.st_copy));
+
+    // ---- parameter staging per chunk (host callers) ----
+    auto upload_chunk = [&](int c) -> int {
+        if (mem == FLASHGMM_MEM_HOST) {
+            for (int a = 0; a < na; ++a) {
+                const flashgmm_stream& s = streams[act[a]];
+                if (s.n <= bound[c]) continue;
+                const int64_t c0 = bound[c], cnt = std::min(s.n, bound[c + 1]) - c0;
+                float* b = d_par + par_off[a];
+                const float* src[3] = {s.scales, s.means, s.weights};
+                for (int t = 0; t < 3; ++t) {
+                    float* dst = b + 4 * npad[a] * t;
+                    if (s.stride_n == 1)
+                        CU_TRY(cudaMemcpy2DAsync(dst + c0, npad[a] * 4, src[t] + c0, (size_t)s.stride_k * 4,
+                                                 (size_t)cnt * 4, 4, cudaMemcpyHostToDevice, D.st_copy));
+                    else
+                        CU_TRY(cudaMemcpyAsync(dst + 4 * c0, src[t] + 4 * c0, (size_t)cnt * 16, cudaMemcpyHostToDevice,
+                                               D.st_copy));
+                }
+            }
+        }
+        CU_TRY(cudaEventRecord(D.ev_up[c], D.st_copy));
+        return FLASHGMM_OK;
+    };
+
+    auto launch_rows = [&](int c) -> int {
+        CU_TRY(cudaStreamWaitEvent(D.st_rows, D.ev_up[c], 0));
+        if (c >= 2) CU_TRY(cudaStreamWaitEvent(D.st_rows, D.ev_pop[c - 2], 0));
+        if (prof) CU_TRY(cudaEventRecord(D.t0[2 * c], D.st_rows));
+        CU_TRY(launch_gmm_cdf_rows_batched(d_rd + ci[c].first, ci[c].count, ci[c].blocks, S, max_row_words, lane_slots,
+                                           mode, D.st_rows));
+        if (prof) CU_TRY(cudaEventRecord(D.t1[2 * c], D.st_rows));
+        CU_TRY(cudaEventRecord(D.ev_rows[c], D.st_rows));
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        return FLASHGMM_OK;
+    };
+    auto launch_pop = [&](int c) -> int {
+        CU_TRY(cudaStreamWaitEvent(D.st_pop, D.ev_rows[c], 0));
+        if (c == 0) CU_TRY(cudaStreamWaitEvent(D.st_pop, D.ev_words, 0));
+        if (prof) CU_TRY(cudaEventRecord(D.t0[2 * c + 1], D.st_pop));
+        CU_TRY(launch_gmm_pop_rows(d_pd + ci[c].first, ci[c].count, lane_slots, mode, D.st_pop));
+        if (prof) CU_TRY(cudaEventRecord(D.t1[2 * c + 1], D.st_pop));
+        CU_TRY(cudaEventRecord(D.ev_pop[c], D.st_pop));
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        return FLASHGMM_OK;
+    };
+
+    // first rows launch goes out before the bitstreams are staged: the GPU works while the host copies
+    if ((rc = upload_chunk(0))) return rc;
+    if ((rc = launch_rows(0))) return rc;
+    {
+        uint32_t* hw = static_cast<uint32_t*>(D.h_words.p);
+        for (int a = 0; a < na; ++a) {
+            const flashgmm_stream& s = streams[act[a]];
+            memcpy(hw + word_off[a], s.bytes, s.bytes_cap / 4 * 4);
+        }
+        CU_TRY(cudaMemcpyAsync(D.words.p, D.h_words.p, total_words * 4, cudaMemcpyHostToDevice, D.st_copy));
+        CU_TRY(cudaEventRecord(D.ev_words, D.st_copy));
+    }
+    for (int c = 0; c < nch; ++c) {
+        if (c + 1 < nch) {
+            if ((rc = upload_chunk(c + 1))) return rc;
+            if ((rc = launch_rows(c + 1))) return rc;
+        }
+        if ((rc = launch_pop(c))) return rc;
+    }
+    CU_TRY(cudaMemcpyAsync(D.h_state.p, D.state.p, (size_t)na * 16, cudaMemcpyDeviceToHost, D.st_pop));
+    if (mem == FLASHGMM_MEM_HOST)
+        for (int a = 0; a < na; ++a) {
+            const flashgmm_stream& s = streams[act[a]];
+            CU_TRY(cudaMemcpyAsync(s.symbols_out, d_out + out_off[a], (size_t)s.n * 4, cudaMemcpyDeviceToHost, D.st_pop));
+        }
+    CU_TRY(cudaStreamSynchronize(D.st_pop));
+    CU_TRY(cudaStreamSynchronize(D.st_rows));
+    CU_TRY(cudaStreamSynchronize(D.st_copy));
+
+    if (prof) {
+        std::lock_guard<std::mutex> pg(g_prof_mu);
+        for (int c = 0; c < nch; ++c) {
+            float ms = 0;
+            double rows_b = 0, pop_b = 0;
+            for (int k = ci[c].first; k < ci[c].first + ci[c].count; ++k) {
+                rows_b += (48.0 + (double)rec_bytes) * h_rd[k].n;
+                pop_b += ((double)rec_bytes + 4.0) * h_rd[k].n;
+            }
+            if (cudaEventElapsedTime(&ms, D.t0[2 * c], D.t1[2 * c]) == cudaSuccess) {
+                g_prof_ms[PROF_TABLE] += ms; g_prof_bytes[PROF_TABLE] += rows_b; g_prof_launches[PROF_TABLE] += 1;
+            }
+            if (cudaEventElapsedTime(&ms, D.t0[2 * c + 1], D.t1[2 * c + 1]) == cudaSuccess) {
+                g_prof_ms[PROF_POP] += ms; g_prof_bytes[PROF_POP] += pop_b; g_prof_launches[PROF_POP] += 1;
+            }
+        }
+    }
+    const uint64_t* hs = static_cast<const uint64_t*>(D.h_state.p);
+    for (int a = 0; a < na; ++a) {
+        flashgmm_stream& s = streams[act[a]];
+        if ((hs[2 * a + 1] >> 32) != 0) {
+            s.status = fail(FLASHGMM_ETRUNC, "bitstream truncated: decoder read past %zu bytes", s.bytes_cap);
+            worst = s.status;
+        }
+    }
+    return worst;
+}
+
+bool want_device_pop(const flashgmm_ctx* ctx, const flashgmm_stream* streams, int n_streams) {
+    if (n_streams < ctx->pop_min_streams) return false;
+    for (int i = 0; i < n_streams; ++i)
+        if (streams[i].max_bs_value > kMaxDevicePopR) return false;
+    return true;
+}
+
 typedef int (*stream_fn)(flashgmm_ctx*, Lane&, flashgmm_stream&, int, int);
 
 int run_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem, stream_fn fn) {
@@ -522,7 +840,7 @@ void flashgmm_profile_reset(void) {
 }
 
 int flashgmm_profile_read(int kind, double* total_ms, uint64_t* launches, double* algorithmic_bytes) {
-    if (kind < 0 || kind >= PROF_KINDS) return fail(FLASHGMM_EINVAL, "kind must be 0 (startfreq), 1 (cdf_table), 2 (ileave encode) or 3 (ileave decode)");
+    if (kind < 0 || kind >= PROF_KINDS) return fail(FLASHGMM_EINVAL, "kind must be 0 (startfreq), 1 (cdf rows), 2 (ileave encode), 3 (ileave decode) or 4 (pop)");
     std::lock_guard<std::mutex> g(g_prof_mu);
     if (total_ms) *total_ms = g_prof_ms[kind];
     if (launches) *launches = g_prof_launches[kind];
@@ -554,6 +872,8 @@ int flashgmm_ctx_create(int device, flashgmm_ctx** out) {
     c->dec_chunk_bytes = std::max<long>(1 << 16, env_long("FLASHGMM_DEC_CHUNK_BYTES", 16 << 20));
     long hw = (long)std::thread::hardware_concurrency();
     c->n_workers = (int)std::max<long>(1, env_long("FLASHGMM_WORKERS", std::min<long>(16, hw > 1 ? hw - 1 : 1)));
+    c->pop_min_streams = (int)std::max<long>(1, env_long("FLASHGMM_POP_MIN_STREAMS", 4));
+    c->pop_rows_budget = std::max<long>(1 << 20, env_long("FLASHGMM_POP_ROWS_BYTES", 512l << 20));
     rcp_table();
     *out = c;
     return FLASHGMM_OK;
@@ -564,6 +884,7 @@ void flashgmm_ctx_destroy(flashgmm_ctx* ctx) {
     ctx->pool.reset();
     cudaSetDevice(ctx->device);
     for (auto& l : ctx->lanes) l->destroy();
+    if (ctx->dd) ctx->dd->destroy();
     ctx->il_scratch.release(); ctx->il_segw.release(); ctx->il_out.release(); ctx->il_err.release();
     ctx->il_host.release();
     delete ctx;
@@ -636,6 +957,7 @@ int flashgmm_gmm_decode(flashgmm_ctx* ctx, const uint8_t* encoded, size_t encode
     s.max_bs_value = max_bs_value;
     s.bytes = const_cast<uint8_t*>(encoded); s.bytes_cap = encoded_len;
     s.symbols_out = symbols_out;
+    if (ctx && want_device_pop(ctx, &s, 1)) return decode_batch_device(ctx, &s, 1, mode, mem);
     return run_batch(ctx, &s, 1, mode, mem, decode_stream);
 }
 
@@ -644,6 +966,9 @@ int flashgmm_gmm_encode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
 }
 
 int flashgmm_gmm_decode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem) {
+    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
+    if (n_streams < 0 || (n_streams > 0 && !streams)) return fail(FLASHGMM_EINVAL, "bad stream array");
+    if (want_device_pop(ctx, streams, n_streams)) return decode_batch_device(ctx, streams, n_streams, mode, mem);
     return run_batch(ctx, streams, n_streams, mode, mem, decode_stream);
 }
 

@@ -132,15 +132,14 @@ constexpr int kLutBuckets = 32;
 constexpr int kLutShift = 11;
 
 template <int MODE>
-__global__ void __launch_bounds__(kRowThreads)
-gmm_cdf_rows_kernel(GmmParamsView p, int64_t n, int R, uint32_t* __restrict__ table32, int row_words,
-                    int lut_off, int S) {
-    extern __shared__ uint32_t smem_u32[];
+__device__ __forceinline__ void
+gmm_cdf_rows_block(const GmmParamsView& p, int64_t n, int R, uint32_t* __restrict__ table32, int row_words,
+                   int lut_off, int S, int64_t block, uint32_t* smem_u32, int lane_slots = 0) {
     float* prm = reinterpret_cast<float*>(smem_u32);       // [12][S]: sg[4], mu[4], w[4]
     uint32_t* tile = smem_u32 + 12 * S;                    // [S][row_words]
     uint32_t* bad = tile + (size_t)S * row_words;          // [S]
 
-    const int64_t row0 = (int64_t)blockIdx.x * S;
+    const int64_t row0 = block * S;
     const int live = (int)min((int64_t)S, n - row0);
     const int W = 2 * R + 2;
 
@@ -206,7 +205,27 @@ gmm_cdf_rows_kernel(GmmParamsView p, int64_t n, int R, uint32_t* __restrict__ ta
         }
         __syncthreads();
     }
-    {
+    if (lane_slots > 0) {
+        // Lane-row record for the device pop kernel (gmm_pop.cu): per symbol `lane_slots` uint32
+        // words, word l*NI + k (NI = lane_slots / 32) = start | width << 16 of interval
+        // j = l + 32k, i.e. T[j] | (T[j+1] - T[j]) << 16 -- lane l reads its NI intervals with one
+        // vector load. Slots past 2R, and every slot of a row that is not monotone, hold
+        // (65535, 0): no lane can hit, the pop kernel then evaluates the reference's search itself.
+        uint32_t* dst = table32 + row0 * lane_slots;
+        const int ni = lane_slots >> 5;
+        for (int id = threadIdx.x; id < live * lane_slots; id += kRowThreads) {
+            const int s = id / lane_slots, t = id - s * lane_slots;
+            const int l = t / ni, k = t - l * ni;
+            const int j = l + 32 * k;
+            const uint16_t* row16 = reinterpret_cast<const uint16_t*>(tile + (size_t)s * row_words);
+            uint32_t v = 65535u;
+            if (j <= 2 * R && bad[s] == 0) {
+                const uint32_t lo = row16[j], hi = row16[j + 1];
+                v = lo | ((hi - lo) << 16);
+            }
+            __stcs(dst + id, v);
+        }
+    } else {
         uint32_t* dst = table32 + row0 * row_words;
         int s = threadIdx.x / row_words, wd = threadIdx.x - s * row_words;
         const int flag_word = W >> 1;
@@ -218,6 +237,31 @@ gmm_cdf_rows_kernel(GmmParamsView p, int64_t n, int R, uint32_t* __restrict__ ta
             if (wd >= row_words) { wd -= row_words; ++s; }
         }
     }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kRowThreads)
+gmm_cdf_rows_kernel(GmmParamsView p, int64_t n, int R, uint32_t* __restrict__ table32, int row_words,
+                    int lut_off, int S) {
+    extern __shared__ uint32_t smem_u32[];
+    gmm_cdf_rows_block<MODE>(p, n, R, table32, row_words, lut_off, S, (int64_t)blockIdx.x, smem_u32);
+}
+
+// Every (stream, chunk) entry of a batch in ONE launch: blockIdx.x -> entry by binary
+// search over the entries' first_block prefix, then the same block body.
+template <int MODE>
+__global__ void __launch_bounds__(kRowThreads)
+gmm_cdf_rows_batched_kernel(const RowsDesc* __restrict__ descs, int n_desc, int S, int lane_slots) {
+    extern __shared__ uint32_t smem_u32[];
+    int lo = 0, hi = n_desc - 1;
+    const int b = (int)blockIdx.x;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (descs[mid].first_block <= b) lo = mid; else hi = mid - 1;
+    }
+    const RowsDesc d = descs[lo];
+    gmm_cdf_rows_block<MODE>(d.p, (int64_t)d.n, d.R, d.table32, d.row_words, -1, S,
+                             (int64_t)(b - d.first_block), smem_u32, lane_slots);
 }
 
 inline int grid_for(int64_t work, int threads) {
@@ -296,6 +340,19 @@ cudaError_t launch_rows_mode(const GmmParamsView& p, int64_t n, int R, uint16_t*
     return cudaGetLastError();
 }
 }  // namespace
+
+cudaError_t launch_gmm_cdf_rows_batched(const RowsDesc* descs_d, int n_desc, int total_blocks, int S,
+                                        int max_row_words, int lane_slots, int mode, cudaStream_t st) {
+    if (n_desc <= 0 || total_blocks <= 0) return cudaSuccess;
+    const size_t smem = (size_t)S * (12 + max_row_words + 1) * 4;
+    if (smem > 48 * 1024) return cudaErrorInvalidValue;      // callers size S for the widest row
+    switch (mode) {
+    case MODE_AS: gmm_cdf_rows_batched_kernel<MODE_AS><<<total_blocks, kRowThreads, smem, st>>>(descs_d, n_desc, S, lane_slots); break;
+    case MODE_LOGISTIC: gmm_cdf_rows_batched_kernel<MODE_LOGISTIC><<<total_blocks, kRowThreads, smem, st>>>(descs_d, n_desc, S, lane_slots); break;
+    default: gmm_cdf_rows_batched_kernel<MODE_POLYA><<<total_blocks, kRowThreads, smem, st>>>(descs_d, n_desc, S, lane_slots);
+    }
+    return cudaGetLastError();
+}
 
 cudaError_t launch_gmm_cdf_table(const GmmParamsView& p, int64_t n, int mode, int R, uint16_t* table,
                                  int row_stride, bool with_lut, cudaStream_t st) {

@@ -31,6 +31,39 @@ int gmm_table_lut_offset(int R);
 cudaError_t launch_gmm_cdf_table(const GmmParamsView& p, int64_t n, int mode, int R, uint16_t* table,
                                  int row_stride, bool with_lut, cudaStream_t st);
 
+// ---- device-resident decode: batched rows + one-warp-per-stream pop (gmm_pop.cu) ----
+// One entry per (stream, chunk): the chunk's rows are produced by the batched rows kernel
+// and consumed by the pop kernel. Plain device pointers; arrays live in device memory.
+struct RowsDesc {
+    GmmParamsView p;          // already offset to the chunk's first symbol
+    uint32_t* table32;        // rows out
+    int32_t n;                // symbols in this chunk
+    int32_t R;
+    int32_t row_words;        // compact row (internal tile) width in uint32
+    int32_t first_block;      // exclusive prefix of ceil(n / S) over the launch's entries
+};
+struct PopDesc {
+    const uint16_t* rows;     // lane-row records (gmm_kernels.cu), 16-byte aligned
+    const uint32_t* words;    // the stream's 32-bit words (device copy)
+    int32_t* out;             // decoded symbols of this chunk
+    uint64_t* state;          // [0] = x, [1] = word cursor | overrun << 32 (carried between chunks)
+    GmmParamsView p;          // the chunk's parameters (symbols the lanes cannot place are searched exactly)
+    int32_t n;                // symbols in this chunk (<= 0: nothing to do)
+    int32_t R;
+    uint32_t n_words;
+    int32_t first;            // 1 = initialise the state from the stream's first two words
+};
+constexpr int kPopMaxR = 63;                       // 2R + 1 <= 128 intervals = 4 per lane
+inline int gmm_pop_lane_slots(int max_R) {             // 1, 2 or 4 intervals per lane
+    const int ni = (2 * max_R + 1 + 31) / 32;
+    return 32 * (ni == 3 ? 4 : ni);
+}
+// descs_d[0 .. n_desc) with first_block prefix; total_blocks = sum ceil(n / S).
+// lane_slots == 0: compact rows (row_words uint32 per symbol); > 0: lane-row records.
+cudaError_t launch_gmm_cdf_rows_batched(const RowsDesc* descs_d, int n_desc, int total_blocks, int S,
+                                        int max_row_words, int lane_slots, int mode, cudaStream_t st);
+cudaError_t launch_gmm_pop_rows(const PopDesc* descs_d, int n_desc, int lane_slots, int mode, cudaStream_t st);
+
 // Interleaved multi-lane rANS (gmm_ileave.cu). scratch: n_seg * gmm_ileave_scratch_words()
 // uint16; seg_words: n_seg uint32; out: device buffer for the whole container.
 int64_t gmm_ileave_scratch_words(int seg_log2);
