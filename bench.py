@@ -13,7 +13,10 @@ to reference-compatible single-stream rANS bytes AND decode them back.
 Arms
   b200      : flashgmm_b200 through its public API (C ABI underneath).
               value = inputs resident in HBM; e2e = inputs in pinned host memory,
-              copies inside the timed region.
+              transfers inside the timed region (the kernels pull the page-locked
+              parameters over PCIe themselves; decoded symbols come back by D2H copy).
+              Encode: startfreq kernel -> host push (north_star 4). Decode: rows kernel ->
+              pop kernel, one warp per stream, entirely on the GPU.
   reference : the reference's own compiled CPU extension (oracle/_ref), all host
               threads it can use (one process per stream).
 """
@@ -34,9 +37,11 @@ sys.path.insert(0, str(ROOT))
 ELIC_GROUPS = (16, 16, 32, 64, 192)          # elic_gmm.py:92-93
 LATENT_HW = (32, 48)                         # 512x768 / 16
 N_SETS = 2                                   # rotating batches of images (each batch > 126 MB L2 for B >= 5)
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
-# (profiles/); None until a capture of the current kernel exists.
-NCU_TRAFFIC = {}
+# (dram__bytes_read.sum + dram__bytes_write.sum) / symbols of the captured launch, from the committed
+# ncu --set full captures (profiles/r01_s13_ncu_*.csv); multiplied by the symbols per launch of this
+# run to give `traffic` per launch. None until a capture of the current kernel exists.
+NCU_DRAM_BYTES_PER_SYMBOL = {}
+ALGO_BYTES_PER_SYMBOL = {"gmm_startfreq": 56.0, "gmm_cdf_rows": 48.0 + 256.0, "gmm_pop_rows": 256.0 + 4.0}
 
 
 def elic_stream_sizes():
@@ -136,6 +141,10 @@ def run_b200(args):
     if world != args.gpus:
         if world == 1 and args.gpus > 1:
             raise SystemExit("--gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
+    # host worker threads (serial push of the encoder) are shared by the ranks of one box
+    if world > 1 and "FLASHGMM_WORKERS" not in os.environ:
+        lws = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
+        os.environ["FLASHGMM_WORKERS"] = str(max(1, min(16, (os.cpu_count() or 1) // max(1, lws) - 1)))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -264,21 +273,34 @@ def run_b200(args):
             dist.destroy_process_group()
         return
     total_syms = 2 * nsym * B * args.steps * world
-    rs = [L.flashgmm_gmm_table_row_stride(R) for R in radii[0][0]]
-    h2d = B * sum(n * 52 + n * 48 for n in sizes)
-    d2h = B * sum(n * 4 + 4 + n * r * 2 for n, r in zip(sizes, rs))
+    stream_bytes = sum(s.size for s in streams)                      # last step's bitstreams (whole batch)
+    h2d = B * sum(n * 52 + n * 48 for n in sizes) + stream_bytes     # enc: symbols + params; dec: params + bitstreams
+    d2h = B * sum(n * 4 + 4 + n * 4 for n in sizes) + 16 * B * len(sizes)   # enc: packed records; dec: symbols + state
     peak, peak_src = measured_peak_gbs()
     dom = max(prof, key=lambda k: prof[k]["ms"])
     issue_peak = 148 * 4 * (clocks["sm_mhz"] if clocks else 1965.0) * 1e6      # warp-instructions / s
 
+    notes = {
+        "gmm_startfreq": "FP32-issue-bound by construction (bit-exact IEEE div/sqrt + polynomial exp, 8 Phi per symbol); "
+                         "launches here are per stream and small, the 16 Mi-symbol microbench line is the kernel at size",
+        "gmm_cdf_rows": "FP32-issue-bound by construction (2R+2 = 46 CDF points x 4 components per symbol, ~10 k "
+                        "thread-instructions per symbol); DESIGN.md section 5",
+        "gmm_pop_rows": "latency-bound by construction: the rANS state recurrence is serial per stream, one warp per "
+                        "stream, ~150 cycles per symbol; HBM fraction is not the figure of merit, ns/symbol/stream is",
+    }
+
     def roof(name):
         p = prof[name]
         ach = p["bytes"] / (p["ms"] / 1e3) / 1e9 if p["ms"] > 0 else 0.0
+        per_launch = p["bytes"] / max(1, p["launches"])
+        dram = NCU_DRAM_BYTES_PER_SYMBOL.get(name)
         return {"kernel": name, "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
-                "frac": round(ach / peak, 4), "traffic": NCU_TRAFFIC.get(name), "peak_source": peak_src,
+                "frac": round(ach / peak, 4),
+                "traffic": round(dram * per_launch / ALGO_BYTES_PER_SYMBOL[name]) if dram else None,
+                "algorithmic_bytes_per_launch": round(per_launch), "peak_source": peak_src,
                 "avg_launch_us": round(1e3 * p["ms"] / max(1, p["launches"]), 2), "launches": p["launches"],
                 "share_of_gpu_time": round(p["ms"] / max(1e-9, sum(v["ms"] for v in prof.values())), 3),
-                "note": "FP32-issue-bound by construction (bit-exact IEEE div/sqrt + polynomial exp); see DESIGN.md section 5"}
+                "note": notes[name]}
 
     line = {
         "metric": "GMM rANS enc+dec Msymbols/s (single-stream, reference-compatible bytes)",
@@ -293,7 +315,9 @@ def run_b200(args):
                    "l2": f"inputs rotate over {N_SETS} batches of {B} images = {N_SETS * B * nsym * 52 / 1e6:.0f} MB "
                          "(one batch alone exceeds the 126 MB L2)",
                    "bits_per_symbol": round(bits, 3), "search_radius": radii[0][0][-1],
-                   "host_workers": int(os.environ.get("FLASHGMM_WORKERS", "0")) or "auto(min(16, cores-1))",
+                   "decode": "device-resident (rows kernel -> pop kernel, one warp per stream)",
+                   "encode": "startfreq kernel -> serial push on host worker threads",
+                   "host_workers": int(os.environ.get("FLASHGMM_WORKERS", "0")) or min(16, max(1, (os.cpu_count() or 2) - 1)),
                    "host_cores": os.cpu_count()},
         "encode_ms_per_image": round(1e3 * enc_t / B, 4), "decode_ms_per_image": round(1e3 * dec_t / B, 4),
         "encode_msym_s": round(nsym * B / enc_t / 1e6, 2), "decode_msym_s": round(nsym * B / dec_t / 1e6, 2),
@@ -537,7 +561,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-microbench", action="store_true")
-    ap.add_argument("--images-per-step", type=int, default=8)
+    ap.add_argument("--images-per-step", type=int, default=24,
+                    help="images per step and per GPU (BASELINE.json configs[4] works on 24 images)")
     ap.add_argument("--mode", type=int, default=0, choices=[0, 1, 2], help="APPROX_MODE (reference code numbering)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -188,17 +188,20 @@ private:
 
 // Buffers, streams and events of the device-resident decode path.
 struct DevDecode {
-    cudaStream_t st_rows = nullptr, st_pop = nullptr, st_copy = nullptr;
+    cudaStream_t st_rows = nullptr, st_pop = nullptr, st_copy = nullptr, st_words = nullptr;
     std::vector<cudaEvent_t> ev_rows, ev_pop, ev_up;      // one per chunk (grown on demand)
     std::vector<cudaEvent_t> t0, t1;                      // kernel timing pairs (profiling only)
     cudaEvent_t ev_words = nullptr;
-    DevBuf rows[2], words, desc, state, params, out;
-    PinBuf h_desc, h_words, h_state;
+    DevBuf rows[2], words, desc, state, params, out, seg;
+    PinBuf h_desc, h_words, h_state, h_seg;
     int init() {
         if (st_rows) return FLASHGMM_OK;
-        CU_TRY(cudaStreamCreateWithFlags(&st_rows, cudaStreamNonBlocking));
-        CU_TRY(cudaStreamCreateWithFlags(&st_pop, cudaStreamNonBlocking));
-        CU_TRY(cudaStreamCreateWithFlags(&st_copy, cudaStreamNonBlocking));
+        int lo_prio = 0, hi_prio = 0;                     // the serial pop kernel is the critical path
+        CU_TRY(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
+        CU_TRY(cudaStreamCreateWithPriority(&st_pop, cudaStreamNonBlocking, hi_prio));
+        CU_TRY(cudaStreamCreateWithPriority(&st_rows, cudaStreamNonBlocking, hi_prio < lo_prio ? hi_prio + 1 : lo_prio));
+        CU_TRY(cudaStreamCreateWithPriority(&st_copy, cudaStreamNonBlocking, lo_prio));
+        CU_TRY(cudaStreamCreateWithPriority(&st_words, cudaStreamNonBlocking, hi_prio));
         CU_TRY(cudaEventCreateWithFlags(&ev_words, cudaEventDisableTiming));
         return FLASHGMM_OK;
     }
@@ -227,9 +230,11 @@ struct DevDecode {
         if (st_rows) cudaStreamDestroy(st_rows);
         if (st_pop) cudaStreamDestroy(st_pop);
         if (st_copy) cudaStreamDestroy(st_copy);
-        st_rows = st_pop = st_copy = nullptr; ev_words = nullptr;
+        if (st_words) cudaStreamDestroy(st_words);
+        st_rows = st_pop = st_copy = st_words = nullptr; ev_words = nullptr;
         rows[0].release(); rows[1].release(); words.release(); desc.release(); state.release();
-        params.release(); out.release(); h_desc.release(); h_words.release(); h_state.release();
+        params.release(); out.release(); seg.release(); h_desc.release(); h_words.release(); h_state.release();
+        h_seg.release();
     }
 };
 
@@ -362,6 +367,34 @@ int stage_chunk(Slot& S, const flashgmm_stream& s, int64_t c0, int64_t cnt, bool
     return FLASHGMM_OK;
 }
 
+// Host buffers that are page-locked (cudaHostAlloc / cudaHostRegister, e.g. torch pin_memory)
+// are read by the kernels in place over PCIe: every parameter is read exactly once, in
+// coalesced 128-byte requests, so a staging copy would only add API calls and a second pass.
+// Returns the device alias of `p`, or nullptr when the memory is pageable.
+inline const void* pinned_alias(const void* p) {
+    if (!p) return nullptr;
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (a.type != cudaMemoryTypeHost || !a.devicePointer) return nullptr;
+    return a.devicePointer;
+}
+// All host tensors of a stream pinned? Then fill `v` (and `sym_d`) with their device aliases.
+inline bool zero_copy_view(const flashgmm_stream& s, bool with_symbols, GmmParamsView* v, const int32_t** sym_d) {
+    static const bool off = env_long("FLASHGMM_ZERO_COPY", 1) == 0;
+    if (off || s.n <= 0) return false;
+    const float* sc = static_cast<const float*>(pinned_alias(s.scales));
+    const float* mu = static_cast<const float*>(pinned_alias(s.means));
+    const float* w = static_cast<const float*>(pinned_alias(s.weights));
+    if (!sc || !mu || !w) return false;
+    if (with_symbols) {
+        const int32_t* sy = static_cast<const int32_t*>(pinned_alias(s.symbols));
+        if (!sy) return false;
+        *sym_d = sy;
+    }
+    *v = GmmParamsView{sc, mu, w, s.stride_n, s.stride_k};
+    return true;
+}
+
 inline GmmParamsView device_view(const flashgmm_stream& s, int64_t c0) {
     return GmmParamsView{s.scales + c0 * s.stride_n, s.means + c0 * s.stride_n,
                          s.weights + c0 * s.stride_n, s.stride_n, s.stride_k};
@@ -378,6 +411,9 @@ int encode_stream(flashgmm_ctx* ctx, Lane& L, flashgmm_stream& s, int mode, int 
     const int64_t n = s.n;
     const std::vector<Chunk> plan = plan_chunks(n, ctx->enc_first, ctx->enc_chunk, true);
     const int64_t nch = (int64_t)plan.size();
+    GmmParamsView zc_view{};
+    const int32_t* zc_sym = nullptr;
+    const bool zc = mem == FLASHGMM_MEM_HOST && zero_copy_view(s, true, &zc_view, &zc_sym);
     L.bb.reset((size_t)(n * 9 / 16) + 64);
     RansEncoder64 enc;
     enc.init(&L.bb);
@@ -392,7 +428,11 @@ int encode_stream(flashgmm_ctx* ctx, Lane& L, flashgmm_stream& s, int mode, int 
         uint32_t* d_flag = d_packed + cntp;
         GmmParamsView view;
         const int32_t* sym_d;
-        if (mem == FLASHGMM_MEM_HOST) {
+        if (zc) {
+            view = GmmParamsView{zc_view.scales + c0 * s.stride_n, zc_view.means + c0 * s.stride_n,
+                                 zc_view.weights + c0 * s.stride_n, s.stride_n, s.stride_k};
+            sym_d = zc_sym + c0;
+        } else if (mem == FLASHGMM_MEM_HOST) {
             int r = stage_chunk(S, s, c0, cnt, true, &view, &sym_d);
             if (r) return r;
         } else {
@@ -456,6 +496,9 @@ int decode_stream(flashgmm_ctx* ctx, Lane& L, flashgmm_stream& s, int mode, int 
     const std::vector<Chunk> plan = plan_chunks(n, std::min<int64_t>(cap, ctx->dec_first), cap, false);
     const int64_t nch = (int64_t)plan.size();
 
+    GmmParamsView zc_view{};
+    const int32_t* zc_unused = nullptr;
+    const bool zc = mem == FLASHGMM_MEM_HOST && zero_copy_view(s, false, &zc_view, &zc_unused);
     int32_t* out_h = s.symbols_out;
     if (mem == FLASHGMM_MEM_DEVICE && n > 0) {
         CU_TRY(L.h_dec.need((size_t)n * 4));
@@ -469,7 +512,10 @@ int decode_stream(flashgmm_ctx* ctx, Lane& L, flashgmm_stream& s, int mode, int 
         CU_TRY(S.d_out.need(tab_bytes));
         CU_TRY(S.h_out.need(tab_bytes));
         GmmParamsView view;
-        if (mem == FLASHGMM_MEM_HOST) {
+        if (zc) {
+            view = GmmParamsView{zc_view.scales + c0 * s.stride_n, zc_view.means + c0 * s.stride_n,
+                                 zc_view.weights + c0 * s.stride_n, s.stride_n, s.stride_k};
+        } else if (mem == FLASHGMM_MEM_HOST) {
             const int32_t* unused;
             int r = stage_chunk(S, s, c0, cnt, false, &view, &unused);
             if (r) return r;
@@ -553,6 +599,13 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     if (na == 0) return worst;
 
     std::vector<int32_t> rs(na);
+    std::vector<GmmParamsView> zc(na);                       // host callers: device aliases of page-locked tensors
+    std::vector<char> is_zc(na, 0);
+    if (mem == FLASHGMM_MEM_HOST)
+        for (int a = 0; a < na; ++a) {
+            const int32_t* unused = nullptr;
+            is_zc[a] = zero_copy_view(streams[act[a]], false, &zc[a], &unused) ? 1 : 0;
+        }
     std::vector<size_t> word_off(na), out_off(na), par_off(na), npad(na);
     {
         size_t wo = 0, oo = 0, po = 0;
@@ -594,7 +647,8 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     const int nch = (int)bound.size() - 1;
     if ((rc = D.need_events(nch))) return rc;
     const bool prof = g_prof_on.load(std::memory_order_relaxed) != 0;
-    if (prof && (rc = D.need_timers(2 * (size_t)nch))) return rc;
+    static const bool trace = env_long("FLASHGMM_TRACE", 0) != 0;   // per-chunk timeline on stderr (with profiling on)
+    if (prof && (rc = D.need_timers(3 * (size_t)nch + 1))) return rc;
 
     // ---- device buffers ----
     int64_t max_chunk_bytes = 0;
@@ -609,7 +663,7 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     float* d_par = nullptr;
     if (mem == FLASHGMM_MEM_HOST) {
         CU_TRY(D.out.need((out_off[na - 1] + npad[na - 1]) * 4));
-        CU_TRY(D.params.need((par_off[na - 1] + 12 * npad[na - 1]) * 4));
+        CU_TRY(D.params.need((par_off[na - 1] + 12 * npad[na - 1]) * 4 + 16));
         d_out = static_cast<int32_t*>(D.out.p);
         d_par = static_cast<float*>(D.params.p);
     }
@@ -670,11 +724,55 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
                            D.st_copy));
 
     // ---- parameter staging per chunk (host callers) ----
-    auto upload_chunk = [&](int c) -> int {
-        if (mem == FLASHGMM_MEM_HOST) {
+    // page-locked tensors: one staging kernel per chunk pulls them over PCIe (segments below);
+    // pageable tensors: cudaMemcpy2DAsync per plane group.
+    struct SegRange { int first, count, blocks; };
+    std::vector<SegRange> sr(nch, SegRange{0, 0, 0});
+    CopySeg* d_seg = nullptr;
+    if (mem == FLASHGMM_MEM_HOST) {
+        std::vector<CopySeg> segs;
+        for (int c = 0; c < nch; ++c) {
+            sr[c].first = (int)segs.size();
+            int blocks = 0;
             for (int a = 0; a < na; ++a) {
                 const flashgmm_stream& s = streams[act[a]];
-                if (s.n <= bound[c]) continue;
+                if (s.n <= bound[c] || !is_zc[a]) continue;
+                const int64_t c0 = bound[c], cnt = std::min(s.n, bound[c + 1]) - c0;
+                float* b = d_par + par_off[a];
+                const float* src[3] = {zc[a].scales, zc[a].means, zc[a].weights};
+                for (int t = 0; t < 3; ++t) {
+                    float* dst = b + 4 * npad[a] * t;
+                    if (s.stride_n == 1) {
+                        for (int k = 0; k < 4; ++k) {
+                            segs.push_back(CopySeg{src[t] + k * s.stride_k + c0, dst + k * npad[a] + c0, (int32_t)cnt, blocks});
+                            blocks += (int)((cnt + kCopySegBlock - 1) / kCopySegBlock);
+                        }
+                    } else {
+                        segs.push_back(CopySeg{src[t] + 4 * c0, dst + 4 * c0, (int32_t)(4 * cnt), blocks});
+                        blocks += (int)((4 * cnt + kCopySegBlock - 1) / kCopySegBlock);
+                    }
+                }
+            }
+            sr[c].count = (int)segs.size() - sr[c].first;
+            sr[c].blocks = blocks;
+        }
+        if (!segs.empty()) {
+            CU_TRY(D.h_seg.need(segs.size() * sizeof(CopySeg)));
+            CU_TRY(D.seg.need(segs.size() * sizeof(CopySeg)));
+            memcpy(D.h_seg.p, segs.data(), segs.size() * sizeof(CopySeg));
+            CU_TRY(cudaMemcpyAsync(D.seg.p, D.h_seg.p, segs.size() * sizeof(CopySeg), cudaMemcpyHostToDevice, D.st_copy));
+            d_seg = static_cast<CopySeg*>(D.seg.p);
+        }
+    }
+    auto upload_chunk = [&](int c) -> int {
+        if (mem == FLASHGMM_MEM_HOST) {
+            if (sr[c].count > 0) {
+                CU_TRY(launch_gmm_stage_segments(d_seg + sr[c].first, sr[c].count, sr[c].blocks, D.st_copy));
+                g_launches.fetch_add(1, std::memory_order_relaxed);
+            }
+            for (int a = 0; a < na; ++a) {
+                const flashgmm_stream& s = streams[act[a]];
+                if (s.n <= bound[c] || is_zc[a]) continue;
                 const int64_t c0 = bound[c], cnt = std::min(s.n, bound[c + 1]) - c0;
                 float* b = d_par + par_off[a];
                 const float* src[3] = {s.scales, s.means, s.weights};
@@ -690,6 +788,7 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
             }
         }
         CU_TRY(cudaEventRecord(D.ev_up[c], D.st_copy));
+        if (prof) CU_TRY(cudaEventRecord(D.t0[2 * nch + c], D.st_copy));
         return FLASHGMM_OK;
     };
 
@@ -715,7 +814,10 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
         return FLASHGMM_OK;
     };
 
-    // first rows launch goes out before the bitstreams are staged: the GPU works while the host copies
+    // The first chunk's staging and rows launch go out first, then the bitstreams (their own stream:
+    // pop(0) must not wait behind the parameter traffic), then every other chunk's staging is
+    // queued on the copy stream: PCIe runs flat out, independent of how far rows -> pop has got.
+    if (prof) CU_TRY(cudaEventRecord(D.t0[3 * nch], D.st_copy));
     if ((rc = upload_chunk(0))) return rc;
     if ((rc = launch_rows(0))) return rc;
     {
@@ -724,14 +826,13 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
             const flashgmm_stream& s = streams[act[a]];
             memcpy(hw + word_off[a], s.bytes, s.bytes_cap / 4 * 4);
         }
-        CU_TRY(cudaMemcpyAsync(D.words.p, D.h_words.p, total_words * 4, cudaMemcpyHostToDevice, D.st_copy));
-        CU_TRY(cudaEventRecord(D.ev_words, D.st_copy));
+        CU_TRY(cudaMemcpyAsync(D.words.p, D.h_words.p, total_words * 4, cudaMemcpyHostToDevice, D.st_words));
+        CU_TRY(cudaEventRecord(D.ev_words, D.st_words));
     }
+    for (int c = 1; c < nch; ++c)
+        if ((rc = upload_chunk(c))) return rc;
     for (int c = 0; c < nch; ++c) {
-        if (c + 1 < nch) {
-            if ((rc = upload_chunk(c + 1))) return rc;
-            if ((rc = launch_rows(c + 1))) return rc;
-        }
+        if (c + 1 < nch && (rc = launch_rows(c + 1))) return rc;
         if ((rc = launch_pop(c))) return rc;
     }
     CU_TRY(cudaMemcpyAsync(D.h_state.p, D.state.p, (size_t)na * 16, cudaMemcpyDeviceToHost, D.st_pop));
@@ -743,7 +844,20 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     CU_TRY(cudaStreamSynchronize(D.st_pop));
     CU_TRY(cudaStreamSynchronize(D.st_rows));
     CU_TRY(cudaStreamSynchronize(D.st_copy));
+    CU_TRY(cudaStreamSynchronize(D.st_words));
 
+    if (prof && trace) {
+        for (int c = 0; c < nch; ++c) {
+            float up = 0, r0 = 0, r1 = 0, p0 = 0, p1 = 0;
+            cudaEventElapsedTime(&up, D.t0[3 * nch], D.t0[2 * nch + c]);
+            cudaEventElapsedTime(&r0, D.t0[3 * nch], D.t0[2 * c]);
+            cudaEventElapsedTime(&r1, D.t0[3 * nch], D.t1[2 * c]);
+            cudaEventElapsedTime(&p0, D.t0[3 * nch], D.t0[2 * c + 1]);
+            cudaEventElapsedTime(&p1, D.t0[3 * nch], D.t1[2 * c + 1]);
+            fprintf(stderr, "[flashgmm trace] chunk %d [%lld,%lld) streams %d: staged %.2f | rows %.2f-%.2f | pop %.2f-%.2f ms\n",
+                    c, (long long)bound[c], (long long)bound[c + 1], ci[c].count, up, r0, r1, p0, p1);
+        }
+    }
     if (prof) {
         std::lock_guard<std::mutex> pg(g_prof_mu);
         for (int c = 0; c < nch; ++c) {

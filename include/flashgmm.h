@@ -17,7 +17,8 @@
  *    stride_k = 1. Any strides are accepted for device memory; host memory must be
  *    one of those two layouts.
  *  - `mem` says where symbols / parameters / decoded output live:
- *    FLASHGMM_MEM_HOST (copied in chunks inside the call, pinned or pageable) or
+ *    FLASHGMM_MEM_HOST (page-locked buffers are read by the kernels in place over PCIe,
+ *    pageable ones are staged in chunks inside the call) or
  *    FLASHGMM_MEM_DEVICE (used in place on the ctx's device). Bitstreams are
  *    always host memory: the serial rANS state recurrence runs on the host.
  *  - `mode` is APPROX_MODE with the reference's CODE numbering (RI:98, 223-233):

@@ -203,3 +203,20 @@ def test_default_ctx_routes_batches_to_the_device_path():
     assert nl.value >= 1 and ms.value > 0
     for o, (sym, *_r) in zip(outs, data):
         assert np.array_equal(o.cpu().numpy(), sym)
+
+
+@pytest.mark.parametrize("n_streams", [1, 6])
+def test_pinned_host_tensors_are_read_in_place(n_streams):
+    """Page-locked host inputs take the zero-copy path (kernels read them over PCIe): same bytes,
+    same symbols as the oracle, for the host-pop path (1 stream) and the device path (6 streams)."""
+    from flashgmm_b200 import batch
+    data = [synth.gmm_numpy(30_000 + 1000 * i + 3, seed=900 + i) for i in range(n_streams)]
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    enc_in = [(pin(sym), kmajor(sg, "cpu"), kmajor(mu, "cpu"), kmajor(w, "cpu")) for sym, sg, mu, w in data]
+    assert all(t.is_pinned() for st in enc_in for t in (st[0], st[1].t()))
+    got = batch.encode_batch(enc_in, 0)
+    want = [port.gmm_encode(sym, sg, mu, w, 0) for sym, sg, mu, w in data]
+    assert got == want
+    outs = batch.decode_batch([(b, st[1], st[2], st[3], synth.search_radius(d[0])) for b, st, d in zip(want, enc_in, data)], 0)
+    for o, d in zip(outs, data):
+        assert o.device.type == "cpu" and np.array_equal(o.numpy(), d[0])
