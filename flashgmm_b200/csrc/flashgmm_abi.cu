@@ -187,13 +187,14 @@ private:
 };
 
 // Buffers, streams and events of the device-resident decode path.
+constexpr int kRowBufs = 4;        // rows run up to 3 chunks ahead of the pop kernel (keeps PCIe / the FP32 pipe busy)
 struct DevDecode {
     cudaStream_t st_rows = nullptr, st_pop = nullptr, st_copy = nullptr, st_words = nullptr;
     std::vector<cudaEvent_t> ev_rows, ev_pop, ev_up;      // one per chunk (grown on demand)
     std::vector<cudaEvent_t> t0, t1;                      // kernel timing pairs (profiling only)
     cudaEvent_t ev_words = nullptr;
-    DevBuf rows[2], words, desc, state, params, out, seg;
-    PinBuf h_desc, h_words, h_state, h_seg;
+    DevBuf rows[kRowBufs], words, desc, state, params, out;
+    PinBuf h_desc, h_words, h_state;
     int init() {
         if (st_rows) return FLASHGMM_OK;
         int lo_prio = 0, hi_prio = 0;                     // the serial pop kernel is the critical path
@@ -232,9 +233,9 @@ struct DevDecode {
         if (st_copy) cudaStreamDestroy(st_copy);
         if (st_words) cudaStreamDestroy(st_words);
         st_rows = st_pop = st_copy = st_words = nullptr; ev_words = nullptr;
-        rows[0].release(); rows[1].release(); words.release(); desc.release(); state.release();
-        params.release(); out.release(); seg.release(); h_desc.release(); h_words.release(); h_state.release();
-        h_seg.release();
+        for (auto& r : rows) r.release();
+        words.release(); desc.release(); state.release();
+        params.release(); out.release(); h_desc.release(); h_words.release(); h_state.release();
     }
 };
 
@@ -615,7 +616,7 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
             word_off[a] = wo; wo += (s.bytes_cap / 4 + 3) / 4 * 4;
             out_off[a] = oo; oo += (size_t)round_up(s.n, 4);
             npad[a] = (size_t)round_up(s.n, 4);
-            par_off[a] = po; po += 12 * npad[a];
+            par_off[a] = po; po += is_zc[a] ? 0 : 12 * npad[a];
         }
     }
     const int max_row_words = gmm_table_lut_offset(max_R) / 2;
@@ -653,8 +654,7 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     // ---- device buffers ----
     int64_t max_chunk_bytes = 0;
     for (int c = 0; c < nch; ++c) max_chunk_bytes = std::max(max_chunk_bytes, chunk_bytes(bound[c], bound[c + 1]));
-    CU_TRY(D.rows[0].need((size_t)max_chunk_bytes));
-    if (nch > 1) CU_TRY(D.rows[1].need((size_t)max_chunk_bytes));
+    for (int b = 0; b < std::min(nch, kRowBufs); ++b) CU_TRY(D.rows[b].need((size_t)max_chunk_bytes));
     CU_TRY(D.words.need(total_words * 4 + 16));
     CU_TRY(D.h_words.need(total_words * 4 + 16));
     CU_TRY(D.state.need((size_t)na * 16));
@@ -684,6 +684,9 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     auto stream_view = [&](int a, int64_t c0) -> GmmParamsView {
         const flashgmm_stream& s = streams[act[a]];
         if (mem == FLASHGMM_MEM_DEVICE) return device_view(s, c0);
+        if (is_zc[a])
+            return GmmParamsView{zc[a].scales + c0 * s.stride_n, zc[a].means + c0 * s.stride_n,
+                                 zc[a].weights + c0 * s.stride_n, s.stride_n, s.stride_k};
         float* b = d_par + par_off[a];
         if (s.stride_n == 1)
             return GmmParamsView{b + c0, b + 4 * npad[a] + c0, b + 8 * npad[a] + c0, 1, (int64_t)npad[a]};
@@ -695,7 +698,7 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
             ci[c].first = (int)k;
             int blocks = 0;
             size_t roff = 0;
-            char* rbase = static_cast<char*>(D.rows[c & 1].p);
+            char* rbase = static_cast<char*>(D.rows[c % kRowBufs].p);
             for (int a = 0; a < na; ++a) {
                 const flashgmm_stream& s = streams[act[a]];
                 if (s.n <= bound[c]) continue;
@@ -723,53 +726,11 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     CU_TRY(cudaMemcpyAsync(D.desc.p, D.h_desc.p, rows_desc_bytes + n_desc * sizeof(PopDesc), cudaMemcpyHostToDevice,
                            D.st_copy));
 
-    // ---- parameter staging per chunk (host callers) ----
-    // page-locked tensors: one staging kernel per chunk pulls them over PCIe (segments below);
-    // pageable tensors: cudaMemcpy2DAsync per plane group.
-    struct SegRange { int first, count, blocks; };
-    std::vector<SegRange> sr(nch, SegRange{0, 0, 0});
-    CopySeg* d_seg = nullptr;
-    if (mem == FLASHGMM_MEM_HOST) {
-        std::vector<CopySeg> segs;
-        for (int c = 0; c < nch; ++c) {
-            sr[c].first = (int)segs.size();
-            int blocks = 0;
-            for (int a = 0; a < na; ++a) {
-                const flashgmm_stream& s = streams[act[a]];
-                if (s.n <= bound[c] || !is_zc[a]) continue;
-                const int64_t c0 = bound[c], cnt = std::min(s.n, bound[c + 1]) - c0;
-                float* b = d_par + par_off[a];
-                const float* src[3] = {zc[a].scales, zc[a].means, zc[a].weights};
-                for (int t = 0; t < 3; ++t) {
-                    float* dst = b + 4 * npad[a] * t;
-                    if (s.stride_n == 1) {
-                        for (int k = 0; k < 4; ++k) {
-                            segs.push_back(CopySeg{src[t] + k * s.stride_k + c0, dst + k * npad[a] + c0, (int32_t)cnt, blocks});
-                            blocks += (int)((cnt + kCopySegBlock - 1) / kCopySegBlock);
-                        }
-                    } else {
-                        segs.push_back(CopySeg{src[t] + 4 * c0, dst + 4 * c0, (int32_t)(4 * cnt), blocks});
-                        blocks += (int)((4 * cnt + kCopySegBlock - 1) / kCopySegBlock);
-                    }
-                }
-            }
-            sr[c].count = (int)segs.size() - sr[c].first;
-            sr[c].blocks = blocks;
-        }
-        if (!segs.empty()) {
-            CU_TRY(D.h_seg.need(segs.size() * sizeof(CopySeg)));
-            CU_TRY(D.seg.need(segs.size() * sizeof(CopySeg)));
-            memcpy(D.h_seg.p, segs.data(), segs.size() * sizeof(CopySeg));
-            CU_TRY(cudaMemcpyAsync(D.seg.p, D.h_seg.p, segs.size() * sizeof(CopySeg), cudaMemcpyHostToDevice, D.st_copy));
-            d_seg = static_cast<CopySeg*>(D.seg.p);
-        }
-    }
+    // ---- parameter staging per chunk (host callers with pageable tensors) ----
+    // page-locked tensors are not staged at all: the rows kernel reads them in place over PCIe
+    // (each parameter exactly once, 128-byte coalesced requests, thousands of warps in flight).
     auto upload_chunk = [&](int c) -> int {
         if (mem == FLASHGMM_MEM_HOST) {
-            if (sr[c].count > 0) {
-                CU_TRY(launch_gmm_stage_segments(d_seg + sr[c].first, sr[c].count, sr[c].blocks, D.st_copy));
-                g_launches.fetch_add(1, std::memory_order_relaxed);
-            }
             for (int a = 0; a < na; ++a) {
                 const flashgmm_stream& s = streams[act[a]];
                 if (s.n <= bound[c] || is_zc[a]) continue;
@@ -794,7 +755,7 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
 
     auto launch_rows = [&](int c) -> int {
         CU_TRY(cudaStreamWaitEvent(D.st_rows, D.ev_up[c], 0));
-        if (c >= 2) CU_TRY(cudaStreamWaitEvent(D.st_rows, D.ev_pop[c - 2], 0));
+        if (c >= kRowBufs) CU_TRY(cudaStreamWaitEvent(D.st_rows, D.ev_pop[c - kRowBufs], 0));
         if (prof) CU_TRY(cudaEventRecord(D.t0[2 * c], D.st_rows));
         CU_TRY(launch_gmm_cdf_rows_batched(d_rd + ci[c].first, ci[c].count, ci[c].blocks, S, max_row_words, lane_slots,
                                            mode, D.st_rows));
@@ -814,9 +775,9 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
         return FLASHGMM_OK;
     };
 
-    // The first chunk's staging and rows launch go out first, then the bitstreams (their own stream:
-    // pop(0) must not wait behind the parameter traffic), then every other chunk's staging is
-    // queued on the copy stream: PCIe runs flat out, independent of how far rows -> pop has got.
+    // The first chunk's rows launch goes out first, then the bitstreams (their own stream: pop(0)
+    // must not wait behind parameter traffic), then the staging copies of pageable tensors; rows
+    // kernels are queued up to kRowBufs - 1 chunks ahead of the pop kernel.
     if (prof) CU_TRY(cudaEventRecord(D.t0[3 * nch], D.st_copy));
     if ((rc = upload_chunk(0))) return rc;
     if ((rc = launch_rows(0))) return rc;
@@ -831,8 +792,10 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     }
     for (int c = 1; c < nch; ++c)
         if ((rc = upload_chunk(c))) return rc;
+    for (int c = 1; c < std::min(nch, kRowBufs - 1); ++c)
+        if ((rc = launch_rows(c))) return rc;
     for (int c = 0; c < nch; ++c) {
-        if (c + 1 < nch && (rc = launch_rows(c + 1))) return rc;
+        if (c + kRowBufs - 1 < nch && (rc = launch_rows(c + kRowBufs - 1))) return rc;
         if ((rc = launch_pop(c))) return rc;
     }
     CU_TRY(cudaMemcpyAsync(D.h_state.p, D.state.p, (size_t)na * 16, cudaMemcpyDeviceToHost, D.st_pop));

@@ -341,50 +341,6 @@ cudaError_t launch_rows_mode(const GmmParamsView& p, int64_t n, int R, uint16_t*
 }
 }  // namespace
 
-// Pulls page-locked host floats into device memory: coalesced 128-bit (or 32-bit, for planes
-// that are not 16-byte aligned) reads over PCIe, 16 loads in flight per thread.
-__global__ void __launch_bounds__(256)
-gmm_stage_segments_kernel(const CopySeg* __restrict__ segs, int n_seg, int total_blocks) {
-    // A small persistent grid: ~0.5 MB of reads in flight saturates PCIe, and the SMs' CTA slots
-    // stay free for the rows and pop kernels this copy runs beside.
-    for (int b = (int)blockIdx.x; b < total_blocks; b += (int)gridDim.x) {
-        int lo = 0, hi = n_seg - 1;
-        while (lo < hi) {
-            const int mid = (lo + hi + 1) >> 1;
-            if (segs[mid].first_block <= b) lo = mid; else hi = mid - 1;
-        }
-        const CopySeg g = segs[lo];
-        const int base = (b - g.first_block) * kCopySegBlock;
-        const int cnt = min(kCopySegBlock, g.n - base);
-        const float* src = g.src + base;
-        float* dst = g.dst + base;
-        if ((((uintptr_t)src | (uintptr_t)dst) & 15) == 0) {
-            const int n4 = cnt >> 2;
-            float4 v[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int i = threadIdx.x + 256 * u;
-                if (i < n4) v[u] = __ldcs(reinterpret_cast<const float4*>(src) + i);
-            }
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int i = threadIdx.x + 256 * u;
-                if (i < n4) reinterpret_cast<float4*>(dst)[i] = v[u];
-            }
-            for (int i = (n4 << 2) + threadIdx.x; i < cnt; i += 256) dst[i] = __ldcs(src + i);
-        } else {
-            for (int i = threadIdx.x; i < cnt; i += 256) dst[i] = __ldcs(src + i);
-        }
-    }
-}
-
-cudaError_t launch_gmm_stage_segments(const CopySeg* segs_d, int n_seg, int total_blocks, cudaStream_t st) {
-    if (n_seg <= 0 || total_blocks <= 0) return cudaSuccess;
-    const int grid = total_blocks < 64 ? total_blocks : 64;
-    gmm_stage_segments_kernel<<<grid, 256, 0, st>>>(segs_d, n_seg, total_blocks);
-    return cudaGetLastError();
-}
-
 cudaError_t launch_gmm_cdf_rows_batched(const RowsDesc* descs_d, int n_desc, int total_blocks, int S,
                                         int max_row_words, int lane_slots, int mode, cudaStream_t st) {
     if (n_desc <= 0 || total_blocks <= 0) return cudaSuccess;

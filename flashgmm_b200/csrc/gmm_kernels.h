@@ -53,17 +53,6 @@ struct PopDesc {
     uint32_t n_words;
     int32_t first;            // 1 = initialise the state from the stream's first two words
 };
-// Host -> device staging of page-locked parameters by a kernel (one launch per chunk, no copy-API
-// call per plane): segment = `n` contiguous floats from the host alias `src` to `dst`.
-struct CopySeg {
-    const float* src;
-    float* dst;
-    int32_t n;
-    int32_t first_block;      // exclusive prefix of ceil(n / kCopySegBlock)
-};
-constexpr int kCopySegBlock = 4096;                 // floats per CTA
-cudaError_t launch_gmm_stage_segments(const CopySeg* segs_d, int n_seg, int total_blocks, cudaStream_t st);
-
 constexpr int kPopMaxR = 63;                       // 2R + 1 <= 128 intervals = 4 per lane
 inline int gmm_pop_lane_slots(int max_R) {             // 1, 2 or 4 intervals per lane
     const int ni = (2 * max_R + 1 + 31) / 32;
