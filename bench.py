@@ -41,7 +41,7 @@ N_SETS = 2                                   # rotating batches of images (each 
 # ncu --set full captures (profiles/r01_s13_ncu_*.csv); multiplied by the symbols per launch of this
 # run to give `traffic` per launch. None until a capture of the current kernel exists.
 NCU_DRAM_BYTES_PER_SYMBOL = {"gmm_startfreq": 52.6, "gmm_cdf_rows": 261.6, "gmm_pop_rows": 367.8}
-ALGO_BYTES_PER_SYMBOL = {"gmm_startfreq": 56.0, "gmm_cdf_rows": 48.0 + 256.0, "gmm_pop_rows": 256.0 + 4.0}
+ALGO_BYTES_PER_SYMBOL = {"gmm_startfreq": 56.0, "gmm_cdf_rows": 48.0 + 272.0, "gmm_pop_rows": 272.0 + 4.0}
 
 
 def elic_stream_sizes():

@@ -564,7 +564,7 @@ Lane& lane_of(flashgmm_ctx* ctx, int idx) {
 // rows kernel (all streams of a chunk in one launch) -> pop kernel (one warp per stream);
 // chunk c+1's rows are computed while chunk c is popped. Only bitstreams go up and decoded
 // symbols come down (mem == HOST additionally stages the parameters chunk by chunk).
-constexpr int32_t kMaxDevicePopR = kPopMaxR;   // 4 intervals per lane; wider searches stay on the host path
+constexpr int32_t kMaxDevicePopR = kPopWindowMaxR;   // wider searches stay on the host path
 
 int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem) {
     std::lock_guard<std::mutex> g(ctx->mu);
@@ -620,9 +620,13 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
         }
     }
     const int max_row_words = gmm_table_lut_offset(max_R) / 2;
-    const int lane_slots = gmm_pop_lane_slots(max_R);
-    const int64_t rec_bytes = 4 * (int64_t)lane_slots;             // lane-row record per symbol
-    int S = (int)std::min<int64_t>(32, (48 * 1024) / ((12 + max_row_words + 1) * 4));
+    // windowed records (one interval per lane, any R) unless FLASHGMM_POP_WINDOW=0 asks for the
+    // every-interval lane rows (R <= 63)
+    static const bool windowed_dflt = env_long("FLASHGMM_POP_WINDOW", 1) != 0;
+    const bool windowed = windowed_dflt || max_R > kPopMaxR;
+    const int lane_slots = windowed ? kPopWindowed : gmm_pop_lane_slots(max_R);
+    const int64_t rec_bytes = windowed ? 4 * (int64_t)kPopWindowWords : 4 * (int64_t)lane_slots;   // record per symbol
+    int S = (int)std::min<int64_t>(32, (48 * 1024) / ((12 + max_row_words + 2) * 4));
     if (total_n < 148 * 8 * 32) S = std::min(S, 8);
 
     // ---- chunk boundaries (symbol offsets common to all streams) ----

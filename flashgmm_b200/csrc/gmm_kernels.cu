@@ -205,7 +205,41 @@ gmm_cdf_rows_block(const GmmParamsView& p, int64_t n, int R, uint32_t* __restric
         }
         __syncthreads();
     }
-    if (lane_slots > 0) {
+    if (lane_slots == kPopWindowed) {
+        // Windowed record for the device pop kernel (gmm_pop.cu), any R: the 32 consecutive
+        // intervals [j0, j0 + 32) that hold the most probability mass, one per lane. 68 words:
+        //   word 0      j0 - R (the symbol value of lane 0's interval), words 1..3 zero
+        //   word 4+2l   start T[j0+l]        word 5+2l   width T[j0+l+1] - T[j0+l]
+        // Intervals past 2R, and every interval of a row that is not monotone, are (65535, 0): no
+        // lane can hit. A symbol outside the window is found by the pop kernel's literal search.
+        int* j0s = reinterpret_cast<int*>(bad + S);
+        const int span = 2 * R + 1 - 32;                    // last admissible j0 (<= 0: the row fits)
+        for (int sidx = threadIdx.x; sidx < live; sidx += kRowThreads) {
+            const uint16_t* row16 = reinterpret_cast<const uint16_t*>(tile + (size_t)sidx * row_words);
+            int best = 0, mass = -1;
+            for (int j0 = 0; j0 <= span; ++j0) {
+                const int m = (int)row16[j0 + 32] - (int)row16[j0];
+                if (m > mass) { mass = m; best = j0; }
+            }
+            j0s[sidx] = best;
+        }
+        __syncthreads();
+        uint32_t* dst = table32 + row0 * kPopWindowWords;
+        for (int id = threadIdx.x; id < live * kPopWindowWords; id += kRowThreads) {
+            const int s = id / kPopWindowWords, t = id - s * kPopWindowWords;
+            const int j0 = j0s[s];
+            uint32_t v = 0;
+            if (t == 0) v = (uint32_t)(j0 - R);
+            else if (t >= 4) {
+                const int j = j0 + ((t - 4) >> 1);
+                const uint16_t* row16 = reinterpret_cast<const uint16_t*>(tile + (size_t)s * row_words);
+                const bool ok = j <= 2 * R && bad[s] == 0;
+                const uint32_t lo = ok ? row16[j] : 65535u, hi = ok ? row16[j + 1] : 65535u;
+                v = (t & 1) ? hi - lo : lo;
+            }
+            __stcs(dst + id, v);
+        }
+    } else if (lane_slots > 0) {
         // Lane-row record for the device pop kernel (gmm_pop.cu): per symbol `lane_slots` uint32
         // words, word l*NI + k (NI = lane_slots / 32) = start | width << 16 of interval
         // j = l + 32k, i.e. T[j] | (T[j+1] - T[j]) << 16 -- lane l reads its NI intervals with one
@@ -344,7 +378,7 @@ cudaError_t launch_rows_mode(const GmmParamsView& p, int64_t n, int R, uint16_t*
 cudaError_t launch_gmm_cdf_rows_batched(const RowsDesc* descs_d, int n_desc, int total_blocks, int S,
                                         int max_row_words, int lane_slots, int mode, cudaStream_t st) {
     if (n_desc <= 0 || total_blocks <= 0) return cudaSuccess;
-    const size_t smem = (size_t)S * (12 + max_row_words + 1) * 4;
+    const size_t smem = (size_t)S * (12 + max_row_words + 2) * 4;    // + bad flag + window base per symbol
     if (smem > 48 * 1024) return cudaErrorInvalidValue;      // callers size S for the widest row
     switch (mode) {
     case MODE_AS: gmm_cdf_rows_batched_kernel<MODE_AS><<<total_blocks, kRowThreads, smem, st>>>(descs_d, n_desc, S, lane_slots); break;

@@ -53,13 +53,17 @@ struct PopDesc {
     uint32_t n_words;
     int32_t first;            // 1 = initialise the state from the stream's first two words
 };
-constexpr int kPopMaxR = 63;                       // 2R + 1 <= 128 intervals = 4 per lane
+constexpr int kPopMaxR = 63;                       // lane-row records: 2R + 1 <= 128 intervals = 4 per lane
+constexpr int kPopWindowed = 1;                    // lane_slots value selecting the windowed record (any R)
+constexpr int kPopWindowWords = 68;                // 272 bytes per symbol
+constexpr int kPopWindowMaxR = 1023;
 inline int gmm_pop_lane_slots(int max_R) {             // 1, 2 or 4 intervals per lane
     const int ni = (2 * max_R + 1 + 31) / 32;
     return 32 * (ni == 3 ? 4 : ni);
 }
 // descs_d[0 .. n_desc) with first_block prefix; total_blocks = sum ceil(n / S).
-// lane_slots == 0: compact rows (row_words uint32 per symbol); > 0: lane-row records.
+// lane_slots == 0: compact rows (row_words uint32 per symbol); kPopWindowed: windowed records;
+// 32 / 64 / 128: lane-row records.
 cudaError_t launch_gmm_cdf_rows_batched(const RowsDesc* descs_d, int n_desc, int total_blocks, int S,
                                         int max_row_words, int lane_slots, int mode, cudaStream_t st);
 cudaError_t launch_gmm_pop_rows(const PopDesc* descs_d, int n_desc, int lane_slots, int mode, cudaStream_t st);

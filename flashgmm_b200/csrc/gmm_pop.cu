@@ -43,7 +43,7 @@ namespace flashgmm {
 namespace {
 
 constexpr int kPopStages = 4;
-constexpr int kPopStageBytes = 8192;
+constexpr int kPopStageBytes = 8704;      // 32 windowed records, 32 / 16 lane-row records
 constexpr uint32_t kFull = 0xffffffffu;
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -162,7 +162,6 @@ __device__ __noinline__ SlowResult pop_slow(PopState S, GmmParamsView p, int64_t
     return o;
 }
 
-constexpr int kGroup = 8;            // symbols between two looks at the "stuck" flag
 constexpr int kWinWords = 128;       // shared-memory window over the stream's words (4 blocks of 32)
 
 // this lane's NI interval words (start | width << 16) of the row at shared address `a`
@@ -177,17 +176,28 @@ __device__ __forceinline__ void lds_row(uint32_t a, uint32_t (&w)[NI]) {
     }
 }
 
-// Record of one symbol: 32 lanes x NI uint32 words, word l*NI + k = start | width << 16 of
-// interval l + 32k  (128*NI bytes).
-template <int NI>
+// One interval of a lane, ready for the hit test.
+struct Ival { uint32_t lo, wd; };
+
+// Record of one symbol
+//   WIN == false: 32 lanes x NI uint32 words, word l*NI + k = start | width << 16 of interval
+//                 l + 32k (128*NI bytes): every interval of the row, R <= 63;
+//   WIN == true : windowed record (NI == 1, 272 bytes, any R): word 0 = symbol value of lane 0's
+//                 interval, then {start, width} as two uint32 per lane for the 32 consecutive
+//                 intervals that hold the most mass -- one LDS.64 and no unpacking per symbol.
+template <int NI, bool WIN>
 __global__ void __launch_bounds__(32)
 gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
     extern __shared__ __align__(128) uint8_t ring[];
     __shared__ uint64_t bars[kPopStages];
     __shared__ __align__(16) uint32_t bcast[4];
     __shared__ __align__(16) uint32_t win[kWinWords];
-    constexpr uint32_t kRowBytes = 128u * NI;
-    constexpr int kRps = (kPopStageBytes / kRowBytes) / kGroup * kGroup;   // rows per stage, whole groups
+    static_assert(!WIN || NI == 1, "the windowed record has one interval per lane");
+    constexpr uint32_t kRowBytes = WIN ? 4u * kPopWindowWords : 128u * NI;
+    // symbols between two looks at the "somebody could not be placed" count = rows per stage: the
+    // per-group bookkeeping (~100 instructions) is paid once per 32 symbols
+    constexpr int kGroup = (kPopStageBytes / kRowBytes) >= 32 ? 32 : 16;
+    constexpr int kRps = kGroup;
 
     const PopDesc d = descs[blockIdx.x];
     if (d.n <= 0) return;
@@ -244,13 +254,25 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
     int sym0 = 0;                                                    // chunk-local index of the stage's first symbol
     int vbase[NI];
 #pragma unroll
-    for (int k = 0; k < NI; ++k) vbase[k] = lane + 32 * k - R;
+    for (int k = 0; k < NI; ++k) vbase[k] = WIN ? lane : lane + 32 * k - R;
+    // this lane's intervals of the row at shared address `a` (a = row base + lane offset)
+    auto load_ivals = [&](uint32_t a, Ival (&iv)[NI]) {
+        if constexpr (WIN) {
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(iv[0].lo), "=r"(iv[0].wd) : "r"(a));
+        } else {
+            uint32_t w[NI];
+            lds_row<NI>(a, w);
+#pragma unroll
+            for (int k = 0; k < NI; ++k) { iv[k].lo = w[k] & 0xffffu; iv[k].wd = w[k] >> 16; }
+        }
+    };
+    constexpr uint32_t kLaneOff0 = WIN ? 16u : 0u, kLaneStride = WIN ? 8u : 4u * NI;
 
     for (int st = 0; st < n_stages; ++st) {
         const int slot = st % kPopStages;
         while (!mbar_try_wait(&bars[slot], (uint32_t)(st / kPopStages) & 1u)) {}
         const int cnt = min(kRps, d.n - st * kRps);
-        const uint32_t stage_base = smem_addr(ring + slot * kPopStageBytes) + 4u * NI * lane;   // this lane's words
+        const uint32_t stage_base = smem_addr(ring + slot * kPopStageBytes) + kLaneOff0 + kLaneStride * lane;   // this lane's words
 
         for (int r = 0; r < cnt; r += kGroup) {
             const int g = min(kGroup, cnt - r);
@@ -260,13 +282,18 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
                 // ---- 8 symbols, no branch ----
                 uint32_t xlo = S.xlo, xhi = S.xhi, ptr = S.ptr;
                 uint32_t nhit = 0u;                                 // symbols of the group THIS lane placed
-                uint32_t cur[NI], nxt[NI];
-                lds_row<NI>(rp, cur);
+                Ival cur[NI], nxt[NI];
+                load_ivals(rp, cur);
+                uint32_t v0 = 0, nv0 = 0;                           // windowed: symbol value of lane 0's interval
+                if (WIN) v0 = lds_u32(rp - kLaneOff0 - kLaneStride * lane);
                 uint32_t wnext = lds_u32(win_base + ((ptr << 2) & (4u * kWinWords - 4u)));
 #pragma unroll
                 for (int i = 0; i < kGroup; ++i) {
                     rp += kRowBytes;
-                    if (i + 1 < kGroup) lds_row<NI>(rp, nxt);        // next row: independent of the chain
+                    if (i + 1 < kGroup) {                            // next row: independent of the chain
+                        load_ivals(rp, nxt);
+                        if (WIN) nv0 = lds_u32(rp - kLaneOff0 - kLaneStride * lane);
+                    }
                     const uint32_t cum = xlo & 0xffffu;
                     const uint32_t xs_lo = __funnelshift_r(xlo, xhi, 16), xs_hi = xhi >> 16;
                     uint32_t clo = 0, chi = 0;
@@ -274,13 +301,14 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
                     bool hit = false;
 #pragma unroll
                     for (int k = 0; k < NI; ++k) {
-                        const uint32_t lo = cur[k] & 0xffffu, wd = cur[k] >> 16;
+                        const uint32_t lo = cur[k].lo, wd = cur[k].wd;
                         const uint32_t dk = cum - lo;
                         const uint64_t ck = (uint64_t)wd * xs_lo + dk + ((uint64_t)(wd * xs_hi) << 32);
                         const bool hk = dk < wd;         // never true for cum == 65535: start + width <= 65535
                         if (hk) { clo = (uint32_t)ck; chi = (uint32_t)(ck >> 32); v = vbase[k]; }
                         hit |= hk;
                     }
+                    if (WIN) v += (int)v0;
                     // the winner posts its state, everyone reads it back (the LSU keeps one warp's shared
                     // accesses in program order). If no lane can place cum the slot keeps its old content
                     // and the group runs on with garbage: the hit count comes up short and the group is
@@ -299,6 +327,7 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
                     if (need) wnext = lds_u32(win_base + ((ptr << 2) & (4u * kWinWords - 4u)));
 #pragma unroll
                     for (int k = 0; k < NI; ++k) cur[k] = nxt[k];
+                    v0 = nv0;
                 }
                 if (__builtin_expect(__reduce_add_sync(kFull, nhit) == (uint32_t)kGroup, 1)) {   // every symbol placed
                     S.xlo = xlo; S.xhi = xhi; S.ptr = ptr;
@@ -315,14 +344,15 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
                     uint32_t clo = 0, chi = 0;
                     int v = 0;
                     bool hit = false;
-                    uint32_t cur[NI];
-                    lds_row<NI>(rp, cur);
+                    Ival cur[NI];
+                    load_ivals(rp, cur);
+                    const int v0 = WIN ? (int)lds_u32(rp - kLaneOff0 - kLaneStride * lane) : 0;
 #pragma unroll
                     for (int k = 0; k < NI; ++k) {
-                        const uint32_t lo = cur[k] & 0xffffu, wd = cur[k] >> 16;
+                        const uint32_t lo = cur[k].lo, wd = cur[k].wd;
                         const uint32_t dk = cum - lo;
                         const uint64_t ck = (uint64_t)wd * xs_lo + dk + ((uint64_t)(wd * xs_hi) << 32);
-                        if (dk < wd) { clo = (uint32_t)ck; chi = (uint32_t)(ck >> 32); v = vbase[k]; hit = true; }
+                        if (dk < wd) { clo = (uint32_t)ck; chi = (uint32_t)(ck >> 32); v = vbase[k] + v0; hit = true; }
                     }
                     const uint32_t rlo = __reduce_or_sync(kFull, clo);
                     const uint32_t rhi = __reduce_or_sync(kFull, chi);
@@ -358,9 +388,10 @@ cudaError_t launch_gmm_pop_rows(const PopDesc* descs_d, int n_desc, int lane_slo
     if (n_desc <= 0) return cudaSuccess;
     const size_t smem = (size_t)kPopStages * kPopStageBytes;
     switch (lane_slots) {
-    case 32: gmm_pop_rows_kernel<1><<<n_desc, 32, smem, st>>>(descs_d, mode); break;
-    case 64: gmm_pop_rows_kernel<2><<<n_desc, 32, smem, st>>>(descs_d, mode); break;
-    case 128: gmm_pop_rows_kernel<4><<<n_desc, 32, smem, st>>>(descs_d, mode); break;
+    case kPopWindowed: gmm_pop_rows_kernel<1, true><<<n_desc, 32, smem, st>>>(descs_d, mode); break;
+    case 32: gmm_pop_rows_kernel<1, false><<<n_desc, 32, smem, st>>>(descs_d, mode); break;
+    case 64: gmm_pop_rows_kernel<2, false><<<n_desc, 32, smem, st>>>(descs_d, mode); break;
+    case 128: gmm_pop_rows_kernel<4, false><<<n_desc, 32, smem, st>>>(descs_d, mode); break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
