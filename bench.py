@@ -40,8 +40,8 @@ N_SETS = 2                                   # rotating batches of images (each 
 # (dram__bytes_read.sum + dram__bytes_write.sum) / symbols of the captured launch, from the committed
 # ncu --set full captures (profiles/r01_s13_ncu_*.csv); multiplied by the symbols per launch of this
 # run to give `traffic` per launch. None until a capture of the current kernel exists.
-NCU_DRAM_BYTES_PER_SYMBOL = {"gmm_startfreq": 52.6, "gmm_cdf_rows": 261.6, "gmm_pop_rows": 367.8}
-ALGO_BYTES_PER_SYMBOL = {"gmm_startfreq": 56.0, "gmm_cdf_rows": 48.0 + 272.0, "gmm_pop_rows": 272.0 + 4.0}
+NCU_DRAM_BYTES_PER_SYMBOL = {"gmm_startfreq": 52.6, "gmm_cdf_rows": 261.6, "gmm_pop_rows": 367.8, "gmm_push": None}
+ALGO_BYTES_PER_SYMBOL = {"gmm_startfreq": 56.0, "gmm_cdf_rows": 48.0 + 272.0, "gmm_pop_rows": 272.0 + 4.0, "gmm_push": 4.0 + 8.0 * 0.14}
 
 
 def elic_stream_sizes():
@@ -224,10 +224,11 @@ def run_b200(args):
     # per-kernel CUDA-event timing in a second pass (events add host work to every launch)
     timed(enc_d, dec_d, max(2, args.steps // 4), profile=True)
     prof = {}
-    for kind, name in ((0, "gmm_startfreq"), (1, "gmm_cdf_rows"), (4, "gmm_pop_rows")):
+    for kind, name in ((0, "gmm_startfreq"), (1, "gmm_cdf_rows"), (4, "gmm_pop_rows"), (5, "gmm_push")):
         ms, n, by = C.c_double(), C.c_uint64(), C.c_double()
         L.flashgmm_profile_read(kind, C.byref(ms), C.byref(n), C.byref(by))
-        prof[name] = dict(ms=ms.value, launches=n.value, bytes=by.value)
+        if n.value:
+            prof[name] = dict(ms=ms.value, launches=n.value, bytes=by.value)
 
     # encode-only / decode-only split on the same inputs (reported beside the headline)
     bs = [[x.copy() for x in enc_d[k].run()] for k in range(N_SETS)]
@@ -286,7 +287,9 @@ def run_b200(args):
         "gmm_cdf_rows": "FP32-issue-bound by construction (2R+2 = 46 CDF points x 4 components per symbol, ~10 k "
                         "thread-instructions per symbol); DESIGN.md section 5",
         "gmm_pop_rows": "latency-bound by construction: the rANS state recurrence is serial per stream, one warp per "
-                        "stream, ~150 cycles per symbol; HBM fraction is not the figure of merit, ns/symbol/stream is",
+                        "stream, ~115 cycles per symbol; HBM fraction is not the figure of merit, ns/symbol/stream is",
+        "gmm_push": "latency-bound by construction: the rANS state recurrence is serial per stream, one warp per "
+                    "stream, ~170 cycles per symbol; runs beside the host worker threads on the shorter streams",
     }
 
     def roof(name):
@@ -316,7 +319,8 @@ def run_b200(args):
                          "(one batch alone exceeds the 126 MB L2)",
                    "bits_per_symbol": round(bits, 3), "search_radius": radii[0][0][-1],
                    "decode": "device-resident (rows kernel -> pop kernel, one warp per stream)",
-                   "encode": "startfreq kernel -> serial push on host worker threads",
+                   "encode": "startfreq kernel -> serial push: the longest streams on host worker threads, the rest on the "
+                             "device (push kernel, one warp per stream), split by a cost model (FLASHGMM_PUSH)",
                    "host_workers": int(os.environ.get("FLASHGMM_WORKERS", "0")) or min(16, max(1, (os.cpu_count() or 2) - 1)),
                    "host_cores": os.cpu_count()},
         "encode_ms_per_image": round(1e3 * enc_t / B, 4), "decode_ms_per_image": round(1e3 * dec_t / B, 4),

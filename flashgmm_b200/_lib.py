@@ -6,8 +6,14 @@ be opened, the calls raise.
 from __future__ import annotations
 
 import ctypes as C
+import os
 import threading
 from pathlib import Path
+
+# ~20 CUDA streams are busy at once (worker threads, device encoder / decoder): give each its own
+# hardware queue. Read by the driver when the CUDA context is created; the library's own constructor
+# does the same for non-Python hosts (csrc/flashgmm_abi.cu). A value set by the user wins.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 PKG = Path(__file__).resolve().parent
 LIB_PATH = PKG / "libflashgmm_b200.so"

@@ -34,7 +34,7 @@ std::atomic<uint64_t> g_launches{0};
 
 // Optional per-kernel timing (bench.py's live roofline): CUDA events around each
 // launch on the launching stream, read back when the chunk is consumed.
-enum { PROF_STARTFREQ = 0, PROF_TABLE = 1, PROF_IL_ENC = 2, PROF_IL_DEC = 3, PROF_POP = 4, PROF_KINDS = 5 };
+enum { PROF_STARTFREQ = 0, PROF_TABLE = 1, PROF_IL_ENC = 2, PROF_IL_DEC = 3, PROF_POP = 4, PROF_PUSH = 5, PROF_KINDS = 6 };
 std::atomic<int> g_prof_on{0};
 std::mutex g_prof_mu;
 double g_prof_ms[PROF_KINDS] = {};
@@ -239,6 +239,28 @@ struct DevDecode {
     }
 };
 
+// Buffers of the device-resident encode path (batched startfreq kernel -> push kernel).
+struct DevEncode {
+    cudaStream_t st = nullptr;
+    cudaEvent_t t[4] = {nullptr, nullptr, nullptr, nullptr};
+    DevBuf packed, scratch, desc, rcp, result;
+    PinBuf h_desc, h_result, h_out;
+    bool rcp_ready = false;
+    int init() {
+        if (st) return FLASHGMM_OK;
+        CU_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        for (auto& e : t) CU_TRY(cudaEventCreate(&e));
+        return FLASHGMM_OK;
+    }
+    void destroy() {
+        if (st) cudaStreamDestroy(st);
+        for (auto& e : t) if (e) { cudaEventDestroy(e); e = nullptr; }
+        st = nullptr; rcp_ready = false;
+        packed.release(); scratch.release(); desc.release(); rcp.release(); result.release();
+        h_desc.release(); h_result.release(); h_out.release();
+    }
+};
+
 }  // namespace
 
 struct flashgmm_ctx {
@@ -256,6 +278,11 @@ struct flashgmm_ctx {
     std::unique_ptr<DevDecode> dd;
     int pop_min_streams = 4;          // batches at least this large decode on the device
     int64_t pop_rows_budget = 512ll << 20;
+    // device-resident encode (startfreq kernel -> push kernel): chosen per call by a cost model
+    std::unique_ptr<DevEncode> de;
+    std::mutex de_mu;                 // the device encode path owns its buffers and stream: it runs beside the workers
+    int push_policy = 0;              // 0 auto, 1 always host workers, 2 always device
+    double push_host_ns = 7.5, push_dev_ns = 87.0;   // per symbol: one host worker / one device warp (measured, B200 box)
 };
 
 namespace {
@@ -860,6 +887,158 @@ bool want_device_pop(const flashgmm_ctx* ctx, const flashgmm_stream* streams, in
     return true;
 }
 
+
+// The library keeps up to ~20 CUDA streams busy at once (one per worker thread, the device
+// encoder's, the device decoder's four). With the driver's default of 8 hardware queues streams
+// share queues, and a copy or event queued behind a long kernel stalls every stream that shares its
+// queue (measured: batch encode 6.1 ms -> 5.0 ms with 32 queues). The setting is read when the
+// CUDA context is created, so it only takes effect if this library is loaded before that; a
+// value set by the user wins.
+__attribute__((constructor)) static void flashgmm_more_hw_queues() {
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
+}
+
+// ---------------- encode a batch of streams entirely on the device ----------------
+// batched startfreq kernel -> push kernel (one warp per stream) -> one D2H of the words.
+// Returns -1 when the batch is not eligible (pageable host tensors): the caller then takes
+// the worker-thread path.
+int encode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem) {
+    std::lock_guard<std::mutex> g(ctx->de_mu);
+    CU_TRY(cudaSetDevice(ctx->device));
+    if (!ctx->de) ctx->de.reset(new DevEncode());
+    DevEncode& E = *ctx->de;
+    int rc = E.init();
+    if (rc) return rc;
+
+    std::vector<int> act;
+    std::vector<GmmParamsView> view(n_streams);
+    std::vector<const int32_t*> sym(n_streams, nullptr);
+    int worst = FLASHGMM_OK;
+    for (int i = 0; i < n_streams; ++i) {
+        flashgmm_stream& s = streams[i];
+        s.bytes_len = 0;
+        s.status = check_gmm_args(s.scales, s.means, s.weights, s.n, s.stride_n, s.stride_k, mode, mem);
+        if (!s.status && s.n > 0 && !s.symbols) s.status = fail(FLASHGMM_EINVAL, "null symbols");
+        if (!s.status && !s.bytes && s.bytes_cap) s.status = fail(FLASHGMM_EINVAL, "null output buffer");
+        if (!s.status && s.n > INT32_MAX / 2) s.status = fail(FLASHGMM_EINVAL, "stream too long for one call");
+        if (s.status) { worst = s.status; continue; }
+        if (mem == FLASHGMM_MEM_DEVICE) {
+            view[i] = device_view(s, 0);
+            sym[i] = s.symbols;
+        } else if (s.n > 0 && !zero_copy_view(s, true, &view[i], &sym[i])) {
+            return -1;
+        }
+        act.push_back(i);
+    }
+    const int na = (int)act.size();
+    if (na == 0) return worst;
+
+    std::vector<size_t> pk_off(na), sc_off(na);
+    size_t pk_total = 0, sc_total = 0;
+    int blocks = 0;
+    for (int a = 0; a < na; ++a) {
+        const flashgmm_stream& s = streams[act[a]];
+        pk_off[a] = pk_total; pk_total += (size_t)round_up(std::max<int64_t>(s.n, 1), 4);
+        sc_off[a] = sc_total; sc_total += s.bytes_cap / 4;
+    }
+    CU_TRY(E.packed.need(pk_total * 4));
+    CU_TRY(E.scratch.need(sc_total * 4 + 16));
+    // words and per-stream results are written by the kernel straight into page-locked host
+    // memory: no copy is queued behind the long push kernel (a dependent entry would stall every
+    // other stream that shares its hardware queue, the worker threads' among them)
+    CU_TRY(E.h_out.need(sc_total * 4 + 16));
+    CU_TRY(E.result.need(16));
+    CU_TRY(E.h_result.need((size_t)na * 32 + 16));
+    const size_t sf_bytes = ((size_t)na * sizeof(SfDesc) + 15) / 16 * 16;
+    CU_TRY(E.desc.need(sf_bytes + (size_t)na * sizeof(PushDesc)));
+    CU_TRY(E.h_desc.need(sf_bytes + (size_t)na * sizeof(PushDesc)));
+    if (!E.rcp_ready) {
+        static_assert(sizeof(PushRcp) == sizeof(RcpEntry), "device table mirrors the host one");
+        CU_TRY(E.rcp.need(65536 * sizeof(PushRcp)));
+        CU_TRY(cudaMemcpyAsync(E.rcp.p, rcp_table(), 65536 * sizeof(PushRcp), cudaMemcpyHostToDevice, E.st));
+        E.rcp_ready = true;
+    }
+    SfDesc* h_sf = static_cast<SfDesc*>(E.h_desc.p);
+    PushDesc* h_pd = reinterpret_cast<PushDesc*>(static_cast<char*>(E.h_desc.p) + sf_bytes);
+    uint32_t* d_packed = static_cast<uint32_t*>(E.packed.p);
+    uint32_t* d_result = static_cast<uint32_t*>(E.h_result.p);
+    unsigned long long* d_used = static_cast<unsigned long long*>(E.result.p);
+    double total_n = 0;
+    for (int a = 0; a < na; ++a) {
+        const flashgmm_stream& s = streams[act[a]];
+        h_sf[a] = SfDesc{view[act[a]], sym[act[a]], d_packed + pk_off[a], (int32_t)s.n, blocks};
+        blocks += (int)((s.n + 127) / 128);
+        h_pd[a] = PushDesc{d_packed + pk_off[a], sym[act[a]], static_cast<uint32_t*>(E.scratch.p) + sc_off[a],
+                           (uint32_t)(s.bytes_cap / 4), (int32_t)s.n, d_result + 8 * (size_t)a};
+        total_n += (double)s.n;
+    }
+    CU_TRY(cudaMemcpyAsync(E.desc.p, E.h_desc.p, sf_bytes + (size_t)na * sizeof(PushDesc), cudaMemcpyHostToDevice, E.st));
+    CU_TRY(cudaMemsetAsync(d_used, 0, 8, E.st));
+    const bool prof = g_prof_on.load(std::memory_order_relaxed) != 0;
+    if (prof) CU_TRY(cudaEventRecord(E.t[0], E.st));
+    CU_TRY(launch_gmm_startfreq_batched(static_cast<const SfDesc*>(E.desc.p), na, blocks, mode, E.st));
+    if (prof) CU_TRY(cudaEventRecord(E.t[1], E.st));
+    CU_TRY(launch_gmm_push(reinterpret_cast<const PushDesc*>(static_cast<char*>(E.desc.p) + sf_bytes), na,
+                           static_cast<const PushRcp*>(E.rcp.p), static_cast<uint32_t*>(E.h_out.p), d_used, E.st));
+    g_launches.fetch_add(2, std::memory_order_relaxed);
+    CU_TRY(cudaStreamSynchronize(E.st));
+    const uint32_t* hr = static_cast<const uint32_t*>(E.h_result.p);
+    unsigned long long used_words = 0;
+    unsigned long long t_first = ~0ull, t_last = 0;
+    for (int a = 0; a < na; ++a) {
+        used_words += std::min<unsigned long long>(hr[8 * a], streams[act[a]].bytes_cap / 4);
+        t_first = std::min(t_first, (unsigned long long)hr[8 * a + 4] | ((unsigned long long)hr[8 * a + 5] << 32));
+        t_last = std::max(t_last, (unsigned long long)hr[8 * a + 6] | ((unsigned long long)hr[8 * a + 7] << 32));
+    }
+    if (prof) {
+        float a = 0;
+        cudaEventElapsedTime(&a, E.t[0], E.t[1]);
+        const double b = (double)(t_last - t_first) * 1e-6;          // the push kernel's own %globaltimer stamps
+        std::lock_guard<std::mutex> pg(g_prof_mu);
+        g_prof_ms[PROF_STARTFREQ] += a; g_prof_bytes[PROF_STARTFREQ] += 56.0 * total_n; g_prof_launches[PROF_STARTFREQ] += 1;
+        g_prof_ms[PROF_PUSH] += b; g_prof_bytes[PROF_PUSH] += 4.0 * total_n + 8.0 * (double)used_words; g_prof_launches[PROF_PUSH] += 1;
+    }
+    const uint32_t* words = static_cast<const uint32_t*>(E.h_out.p);
+    for (int a = 0; a < na; ++a) {
+        flashgmm_stream& s = streams[act[a]];
+        const uint32_t need = hr[8 * a], off = hr[8 * a + 1], over = hr[8 * a + 2];
+        s.bytes_len = (size_t)need * 4;
+        if (over) {
+            s.status = fail(FLASHGMM_ENOSPC, "output buffer too small: need %zu bytes, have %zu", s.bytes_len, s.bytes_cap);
+            worst = s.status;
+        } else {
+            memcpy(s.bytes, words + off, s.bytes_len);
+        }
+    }
+    return worst;
+}
+
+// Host workers or device warps for the serial push? A host worker does ~7.5 ns per symbol, a
+// device warp ~87 ns but every stream has its own. Streams are sorted by length; the `k` longest go
+// to the worker threads, the rest to the device, both at once: k minimises the later finish.
+// (One free box: the long streams stay on the host, the many short ones go to the GPU. Several
+// ranks sharing few cores: most or all of the batch goes to the GPU.)
+int plan_push_split(const flashgmm_ctx* ctx, const flashgmm_stream* streams, int n_streams, std::vector<int>* order) {
+    order->resize(n_streams);
+    for (int i = 0; i < n_streams; ++i) (*order)[i] = i;
+    std::sort(order->begin(), order->end(), [&](int a, int b) { return streams[a].n > streams[b].n; });
+    if (ctx->push_policy == 1 || n_streams < 4) return n_streams;
+    if (ctx->push_policy == 2) return 0;
+    const double workers = (double)std::max(1, ctx->n_workers);
+    double best = 1e300, host_sum = 0;
+    int best_k = n_streams;
+    for (int k = 0; k <= n_streams; ++k) {
+        // host: k longest streams over the workers (never faster than its longest stream)
+        const double host = k == 0 ? 0.0
+            : std::max(host_sum / std::min(workers, (double)k), (double)streams[(*order)[0]].n) * ctx->push_host_ns;
+        const double dev = k == n_streams ? 0.0 : (double)streams[(*order)[k]].n * ctx->push_dev_ns + 2.5e5;
+        const double t = std::max(host, dev);
+        if (t < best) { best = t; best_k = k; }
+        if (k < n_streams) host_sum += (double)streams[(*order)[k]].n;
+    }
+    return best_k;
+}
+
 typedef int (*stream_fn)(flashgmm_ctx*, Lane&, flashgmm_stream&, int, int);
 
 int run_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem, stream_fn fn) {
@@ -921,7 +1100,7 @@ void flashgmm_profile_reset(void) {
 }
 
 int flashgmm_profile_read(int kind, double* total_ms, uint64_t* launches, double* algorithmic_bytes) {
-    if (kind < 0 || kind >= PROF_KINDS) return fail(FLASHGMM_EINVAL, "kind must be 0 (startfreq), 1 (cdf rows), 2 (ileave encode), 3 (ileave decode) or 4 (pop)");
+    if (kind < 0 || kind >= PROF_KINDS) return fail(FLASHGMM_EINVAL, "kind must be 0 (startfreq), 1 (cdf rows), 2 (ileave encode), 3 (ileave decode), 4 (pop) or 5 (push)");
     std::lock_guard<std::mutex> g(g_prof_mu);
     if (total_ms) *total_ms = g_prof_ms[kind];
     if (launches) *launches = g_prof_launches[kind];
@@ -955,6 +1134,10 @@ int flashgmm_ctx_create(int device, flashgmm_ctx** out) {
     c->n_workers = (int)std::max<long>(1, env_long("FLASHGMM_WORKERS", std::min<long>(16, hw > 1 ? hw - 1 : 1)));
     c->pop_min_streams = (int)std::max<long>(1, env_long("FLASHGMM_POP_MIN_STREAMS", 4));
     c->pop_rows_budget = std::max<long>(1 << 20, env_long("FLASHGMM_POP_ROWS_BYTES", 512l << 20));
+    {
+        const char* pp = getenv("FLASHGMM_PUSH");            // host | device | (unset) auto
+        c->push_policy = (pp && pp[0] == 'h') ? 1 : (pp && pp[0] == 'd') ? 2 : 0;
+    }
     rcp_table();
     *out = c;
     return FLASHGMM_OK;
@@ -966,6 +1149,7 @@ void flashgmm_ctx_destroy(flashgmm_ctx* ctx) {
     cudaSetDevice(ctx->device);
     for (auto& l : ctx->lanes) l->destroy();
     if (ctx->dd) ctx->dd->destroy();
+    if (ctx->de) ctx->de->destroy();
     ctx->il_scratch.release(); ctx->il_segw.release(); ctx->il_out.release(); ctx->il_err.release();
     ctx->il_host.release();
     delete ctx;
@@ -1043,7 +1227,31 @@ int flashgmm_gmm_decode(flashgmm_ctx* ctx, const uint8_t* encoded, size_t encode
 }
 
 int flashgmm_gmm_encode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem) {
-    return run_batch(ctx, streams, n_streams, mode, mem, encode_stream);
+    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
+    if (n_streams < 0 || (n_streams > 0 && !streams)) return fail(FLASHGMM_EINVAL, "bad stream array");
+    std::vector<int> order;
+    const int k_host = plan_push_split(ctx, streams, n_streams, &order);
+    if (k_host >= n_streams) return run_batch(ctx, streams, n_streams, mode, mem, encode_stream);
+    // the n_streams - k_host shortest streams on the device (own thread, own CUDA stream) while the
+    // k_host longest are pushed by the worker threads
+    std::vector<flashgmm_stream> dev_part, host_part;
+    for (int j = k_host; j < n_streams; ++j) dev_part.push_back(streams[order[j]]);
+    for (int j = 0; j < k_host; ++j) host_part.push_back(streams[order[j]]);
+    int dev_rc = FLASHGMM_OK;
+    std::string dev_err;
+    std::thread dev_thread([&] {
+        dev_rc = encode_batch_device(ctx, dev_part.data(), (int)dev_part.size(), mode, mem);
+        if (dev_rc > 0) dev_err = g_err;
+    });
+    int host_rc = host_part.empty() ? FLASHGMM_OK
+                                    : run_batch(ctx, host_part.data(), (int)host_part.size(), mode, mem, encode_stream);
+    dev_thread.join();
+    if (dev_rc < 0)                                          // pageable host tensors: the workers take them too
+        dev_rc = run_batch(ctx, dev_part.data(), (int)dev_part.size(), mode, mem, encode_stream);
+    else if (dev_rc > 0) g_err = dev_err;
+    for (int j = 0; j < k_host; ++j) streams[order[j]] = host_part[j];
+    for (int j = k_host; j < n_streams; ++j) streams[order[j]] = dev_part[j - k_host];
+    return host_rc ? host_rc : dev_rc;
 }
 
 int flashgmm_gmm_decode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem) {

@@ -347,6 +347,34 @@ cudaError_t launch_gmm_startfreq(const int32_t* sym, const GmmParamsView& p, int
     }
 }
 
+// Every stream of a batch in one launch (one symbol per thread, any layout).
+template <int MODE>
+__global__ void __launch_bounds__(128)
+gmm_startfreq_batched_kernel(const SfDesc* __restrict__ descs, int n_desc) {
+    int lo = 0, hi = n_desc - 1;
+    const int b = (int)blockIdx.x;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (descs[mid].first_block <= b) lo = mid; else hi = mid - 1;
+    }
+    const SfDesc d = descs[lo];
+    const int i = (b - d.first_block) * 128 + (int)threadIdx.x;
+    if (i >= d.n) return;
+    float mu[4], sg[4], w[4];
+    load_generic(d.p, i, mu, sg, w);
+    d.packed[i] = gmm_startfreq1<MODE>(__ldg(d.sym + i), mu, sg, w);
+}
+
+cudaError_t launch_gmm_startfreq_batched(const SfDesc* descs_d, int n_desc, int total_blocks, int mode, cudaStream_t st) {
+    if (n_desc <= 0 || total_blocks <= 0) return cudaSuccess;
+    switch (mode) {
+    case MODE_AS: gmm_startfreq_batched_kernel<MODE_AS><<<total_blocks, 128, 0, st>>>(descs_d, n_desc); break;
+    case MODE_LOGISTIC: gmm_startfreq_batched_kernel<MODE_LOGISTIC><<<total_blocks, 128, 0, st>>>(descs_d, n_desc); break;
+    default: gmm_startfreq_batched_kernel<MODE_POLYA><<<total_blocks, 128, 0, st>>>(descs_d, n_desc);
+    }
+    return cudaGetLastError();
+}
+
 int gmm_table_lut_offset(int R) { return ((2 * R + 3) + 7) & ~7; }
 
 namespace {

@@ -68,6 +68,32 @@ cudaError_t launch_gmm_cdf_rows_batched(const RowsDesc* descs_d, int n_desc, int
                                         int max_row_words, int lane_slots, int mode, cudaStream_t st);
 cudaError_t launch_gmm_pop_rows(const PopDesc* descs_d, int n_desc, int lane_slots, int mode, cudaStream_t st);
 
+// ---- device-resident encode: batched startfreq + one-warp-per-stream push (gmm_push.cu) ----
+struct SfDesc {
+    GmmParamsView p;
+    const int32_t* sym;
+    uint32_t* packed;         // out: start | freq << 16 per symbol, 0x0000ffff = bypass
+    int32_t n;
+    int32_t first_block;      // exclusive prefix of ceil(n / 128)
+};
+cudaError_t launch_gmm_startfreq_batched(const SfDesc* descs_d, int n_desc, int total_blocks, int mode, cudaStream_t st);
+
+// Exact reciprocal of every 16-bit frequency: q = (umul64hi(x, rcp) >> shift) == x / freq for
+// x < 2^63 (rans_host.hpp::RcpEntry, built on the host, uploaded once per ctx).
+struct PushRcp { unsigned long long rcp; uint32_t cmpl; uint16_t shift; uint16_t bias; };   // == rans_host.hpp::RcpEntry
+struct PushDesc {
+    const uint32_t* packed;   // n records (device)
+    const int32_t* sym;       // symbol values (bypass records only)
+    uint32_t* buf;            // scratch for the stream's words, filled from the end
+    uint32_t cap_words;       // scratch capacity == the caller's output capacity in words
+    int32_t n;
+    uint32_t* result;         // 8 words: [0] words produced (needed, if it overflowed), [1] offset in `out`, [2] overflow, [4..7] %globaltimer at entry / exit
+};
+// All streams' words end up back to back in `out` (claimed with one atomicAdd per stream on
+// *out_used, in words); result[1] says where.
+cudaError_t launch_gmm_push(const PushDesc* descs_d, int n_desc, const PushRcp* rcp_d, uint32_t* out,
+                            unsigned long long* out_used, cudaStream_t st);
+
 // Interleaved multi-lane rANS (gmm_ileave.cu). scratch: n_seg * gmm_ileave_scratch_words()
 // uint16; seg_words: n_seg uint32; out: device buffer for the whole container.
 int64_t gmm_ileave_scratch_words(int seg_log2);

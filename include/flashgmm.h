@@ -101,8 +101,17 @@ int flashgmm_gmm_decode(flashgmm_ctx* ctx, const uint8_t* encoded, size_t encode
                         int32_t* symbols_out);
 
 /* Many independent streams in one call (one per checkerboard pass / channel group /
- * image): kernels are queued back to back and the serial host coding of the
- * streams runs on the ctx's worker threads. */
+ * image). The rANS recurrence is serial within a stream, so the stream is the unit of
+ * parallelism:
+ *   decode: batches of >= 4 streams (FLASHGMM_POP_MIN_STREAMS) with max_bs_value <= 1023 never
+ *           leave the GPU -- a batched rows kernel writes per-symbol interval records, a pop
+ *           kernel walks each stream's state with one warp (gmm_pop.cu); smaller batches and
+ *           larger radii run the rows kernel per stream and pop on the ctx's worker threads;
+ *   encode: one startfreq pass, then the serial push of the longest streams on the worker
+ *           threads and of the rest on the GPU (push kernel, one warp per stream, gmm_push.cu),
+ *           both at once, split by a cost model (FLASHGMM_PUSH=host|device|auto).
+ * Either way the bytes / symbols are the reference's. Page-locked host buffers are read by
+ * the kernels in place; pageable ones are staged. */
 typedef struct {
     const int32_t* symbols;   /* encode: in.  decode: unused (may be NULL) */
     const float* scales;
@@ -224,8 +233,11 @@ uint64_t flashgmm_launch_count(void);
 /* Optional live kernel timing for roofline reports: when enabled, every kernel the
  * whole-call entry points launch is bracketed by CUDA events on its own stream.
  * kind 0 = gmm_startfreq (algorithmic bytes 56/symbol), 1 = gmm_cdf_table
- * (48 + 2*row_stride bytes/symbol), 2 = interleaved encode (52 B/symbol + stream),
- * 3 = interleaved decode (48 B/symbol + stream + 4). */
+ * / the batched rows kernel of the device decoder (48 B/symbol in + the record it writes),
+ * 2 = interleaved encode (52 B/symbol + stream), 3 = interleaved decode (48 B/symbol +
+ * stream + 4), 4 = gmm_pop_rows, the device decoder's serial half (record + 4 B/symbol),
+ * 5 = gmm_push, the device encoder's serial half (4 B/symbol + the words it writes twice;
+ * timed by the kernel's own %globaltimer stamps). */
 void flashgmm_profile_enable(int on);
 void flashgmm_profile_reset(void);
 int flashgmm_profile_read(int kind, double* total_ms, uint64_t* launches, double* algorithmic_bytes);

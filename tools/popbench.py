@@ -29,4 +29,16 @@ for kind, name in ((1, "rows"), (4, "pop")):
     L.flashgmm_profile_read(kind, C.byref(ms), C.byref(n), C.byref(by))
     r[name] = round(ms.value / 5, 3)
 nsym = sum(st[0].numel() for st in flat)
+enc.run(); enc.run()
+L.flashgmm_profile_reset(); L.flashgmm_profile_enable(1)
+torch.cuda.synchronize(); t2 = time.perf_counter()
+for _ in range(5):
+    enc.run()
+torch.cuda.synchronize(); t3 = time.perf_counter()
+L.flashgmm_profile_enable(0)
+for kind, name in ((0, "startfreq"), (5, "push")):
+    ms, n, by = C.c_double(), C.c_uint64(), C.c_double()
+    L.flashgmm_profile_read(kind, C.byref(ms), C.byref(n), C.byref(by))
+    r[name] = round(ms.value / 5, 3)
+r["encode_ms"] = round((t3 - t2) / 5 * 1e3, 3)
 print(json.dumps({"B": B, "decode_ms": round((t1 - t0) / 5 * 1e3, 3), "msym_s": round(nsym / ((t1 - t0) / 5) / 1e6, 1), "kernel_ms_per_call": r}))
