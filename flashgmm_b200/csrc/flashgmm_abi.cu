@@ -110,13 +110,18 @@ struct Slot {
 
 struct Lane {
     Slot slot[kSlots];
+    // ONE CUDA stream per lane, shared by its slots (the slots only rotate buffers and events):
+    // the whole library then stays below the 32 hardware queues it asks for, and no worker's
+    // copy ever queues behind another stream's long kernel (see flashgmm_more_hw_queues).
+    cudaStream_t st = nullptr;
     BackBuffer bb;
     PinBuf h_dec;     // decoded symbols before H2D (device-memory callers)
     bool ready = false;
     int init() {
         if (ready) return FLASHGMM_OK;
+        CU_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
         for (auto& s : slot) {
-            CU_TRY(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
+            s.st = st;
             CU_TRY(cudaEventCreateWithFlags(&s.ev, cudaEventDisableTiming));
             CU_TRY(cudaEventCreate(&s.k0));
             CU_TRY(cudaEventCreate(&s.k1));
@@ -125,8 +130,9 @@ struct Lane {
         return FLASHGMM_OK;
     }
     void destroy() {
+        if (st) cudaStreamDestroy(st);
+        st = nullptr;
         for (auto& s : slot) {
-            if (s.st) cudaStreamDestroy(s.st);
             if (s.ev) cudaEventDestroy(s.ev);
             if (s.k0) cudaEventDestroy(s.k0);
             if (s.k1) cudaEventDestroy(s.k1);
@@ -187,23 +193,25 @@ private:
 };
 
 // Buffers, streams and events of the device-resident decode path.
-constexpr int kRowBufs = 4;        // rows run up to 3 chunks ahead of the pop kernel (keeps PCIe / the FP32 pipe busy)
+constexpr int kRowBufs = 3;        // per group: rows run up to 2 work items ahead of the group's pop kernel
+constexpr int kPopGroups = 6;      // streams are grouped by length; every group has its own pop stream
 struct DevDecode {
-    cudaStream_t st_rows = nullptr, st_pop = nullptr, st_copy = nullptr, st_words = nullptr;
+    cudaStream_t st_rows = nullptr, st_copy = nullptr, st_words = nullptr;
+    cudaStream_t st_pop[kPopGroups] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     std::vector<cudaEvent_t> ev_rows, ev_pop, ev_up;      // one per chunk (grown on demand)
     std::vector<cudaEvent_t> t0, t1;                      // kernel timing pairs (profiling only)
-    cudaEvent_t ev_words = nullptr;
-    DevBuf rows[kRowBufs], words, desc, state, params, out;
+    cudaEvent_t ev_words[kPopGroups] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // a group's bitstreams are up
+    DevBuf rows[kPopGroups][kRowBufs], words, desc, state, params, out;
     PinBuf h_desc, h_words, h_state;
     int init() {
         if (st_rows) return FLASHGMM_OK;
         int lo_prio = 0, hi_prio = 0;                     // the serial pop kernel is the critical path
         CU_TRY(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
-        CU_TRY(cudaStreamCreateWithPriority(&st_pop, cudaStreamNonBlocking, hi_prio));
+        for (auto& sp : st_pop) CU_TRY(cudaStreamCreateWithPriority(&sp, cudaStreamNonBlocking, hi_prio));
         CU_TRY(cudaStreamCreateWithPriority(&st_rows, cudaStreamNonBlocking, hi_prio < lo_prio ? hi_prio + 1 : lo_prio));
         CU_TRY(cudaStreamCreateWithPriority(&st_copy, cudaStreamNonBlocking, lo_prio));
         CU_TRY(cudaStreamCreateWithPriority(&st_words, cudaStreamNonBlocking, hi_prio));
-        CU_TRY(cudaEventCreateWithFlags(&ev_words, cudaEventDisableTiming));
+        for (auto& e : ev_words) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         return FLASHGMM_OK;
     }
     int need_events(size_t n) {
@@ -227,13 +235,13 @@ struct DevDecode {
     }
     void destroy() {
         for (auto v : {&ev_rows, &ev_pop, &ev_up, &t0, &t1}) { for (auto e : *v) cudaEventDestroy(e); v->clear(); }
-        if (ev_words) cudaEventDestroy(ev_words);
+        for (auto& e : ev_words) { if (e) cudaEventDestroy(e); e = nullptr; }
         if (st_rows) cudaStreamDestroy(st_rows);
-        if (st_pop) cudaStreamDestroy(st_pop);
+        for (auto& sp : st_pop) { if (sp) cudaStreamDestroy(sp); sp = nullptr; }
         if (st_copy) cudaStreamDestroy(st_copy);
         if (st_words) cudaStreamDestroy(st_words);
-        st_rows = st_pop = st_copy = st_words = nullptr; ev_words = nullptr;
-        for (auto& r : rows) r.release();
+        st_rows = st_copy = st_words = nullptr;
+        for (auto& gr : rows) for (auto& r : gr) r.release();
         words.release(); desc.release(); state.release();
         params.release(); out.release(); h_desc.release(); h_words.release(); h_state.release();
     }
@@ -246,6 +254,11 @@ struct DevEncode {
     DevBuf packed, scratch, desc, rcp, result;
     PinBuf h_desc, h_result, h_out;
     bool rcp_ready = false;
+    // a batch in flight between encode_batch_device_begin and _finish
+    std::vector<int> act;
+    int worst = FLASHGMM_OK;
+    bool prof = false;
+    double total_n = 0;
     int init() {
         if (st) return FLASHGMM_OK;
         CU_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
@@ -277,7 +290,7 @@ struct flashgmm_ctx {
     // device-resident decode (rows kernel -> pop kernel, nothing but symbols leaves the GPU)
     std::unique_ptr<DevDecode> dd;
     int pop_min_streams = 4;          // batches at least this large decode on the device
-    int64_t pop_rows_budget = 512ll << 20;
+    int64_t pop_rows_budget = 256ll << 20;
     // device-resident encode (startfreq kernel -> push kernel): chosen per call by a cost model
     std::unique_ptr<DevEncode> de;
     std::mutex de_mu;                 // the device encode path owns its buffers and stream: it runs beside the workers
@@ -625,6 +638,16 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     }
     const int na = (int)act.size();
     if (na == 0) return worst;
+    // Streams by length, longest first, cut into groups where the length halves. The longest streams'
+    // pop is the critical path of the call (serial, ~58 ns per symbol): a group's rows are never
+    // made to wait for the rows of shorter streams, and every group pops on its own CUDA stream.
+    std::stable_sort(act.begin(), act.end(), [&](int a, int b) { return streams[a].n > streams[b].n; });
+    std::vector<int> grp_begin{0};
+    for (int a = 1; a < na; ++a)
+        if ((int)grp_begin.size() < kPopGroups && streams[act[a]].n * 2 <= streams[act[grp_begin.back()]].n)
+            grp_begin.push_back(a);
+    const int ng = (int)grp_begin.size();
+    grp_begin.push_back(na);
 
     std::vector<int32_t> rs(na);
     std::vector<GmmParamsView> zc(na);                       // host callers: device aliases of page-locked tensors
@@ -656,36 +679,55 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     int S = (int)std::min<int64_t>(32, (48 * 1024) / ((12 + max_row_words + 2) * 4));
     if (total_n < 148 * 8 * 32) S = std::min(S, 8);
 
-    // ---- chunk boundaries (symbol offsets common to all streams) ----
-    auto chunk_bytes = [&](int64_t lo, int64_t hi) {
+    // ---- work items: (group, symbol range common to the group's streams) ----
+    struct Item { int g; int64_t lo, hi, left; int k, ring_prev; };   // k: index within the group; ring_prev: the item whose row buffer it reuses
+    auto item_bytes = [&](int g, int64_t lo, int64_t hi) {
         int64_t b = 0;
-        for (int a = 0; a < na; ++a) {
+        for (int a = grp_begin[g]; a < grp_begin[g + 1]; ++a) {
             const int64_t n = streams[act[a]].n;
             if (n > lo) b += (std::min(n, hi) - lo) * rec_bytes;
         }
         return b;
     };
-    std::vector<int64_t> bound{0};
-    {
-        int64_t step = 4096;
-        while (bound.back() < max_n) {
-            const int64_t lo = bound.back();
+    std::vector<Item> items;
+    for (int g = 0; g < ng; ++g) {
+        const int64_t gmax = streams[act[grp_begin[g]]].n;
+        int64_t step = 4096, lo = 0;
+        while (lo < gmax) {
             int64_t st = step;
-            while (st > 256 && chunk_bytes(lo, lo + st) > ctx->pop_rows_budget) st /= 2;
-            bound.push_back(std::min(max_n, lo + st));
+            while (st > 256 && item_bytes(g, lo, lo + st) > ctx->pop_rows_budget) st /= 2;
+            const int64_t hi = std::min(gmax, lo + st);
+            items.push_back(Item{g, lo, hi, gmax - lo, 0, -1});
+            lo = hi;
             step = std::min<int64_t>(32768, step * 3);
         }
     }
-    const int nch = (int)bound.size() - 1;
+    // earliest deadline first: the item with the most symbols still to pop behind it is the most
+    // urgent (within a group that is the natural order)
+    std::stable_sort(items.begin(), items.end(), [](const Item& x, const Item& y) { return x.left > y.left; });
+    const int nch = (int)items.size();
+    {
+        std::vector<std::vector<int>> of_group(ng);
+        for (int c = 0; c < nch; ++c) {
+            std::vector<int>& v = of_group[items[c].g];
+            items[c].k = (int)v.size();
+            items[c].ring_prev = items[c].k >= kRowBufs ? v[items[c].k - kRowBufs] : -1;
+            v.push_back(c);
+        }
+    }
     if ((rc = D.need_events(nch))) return rc;
     const bool prof = g_prof_on.load(std::memory_order_relaxed) != 0;
     static const bool trace = env_long("FLASHGMM_TRACE", 0) != 0;   // per-chunk timeline on stderr (with profiling on)
     if (prof && (rc = D.need_timers(3 * (size_t)nch + 1))) return rc;
 
     // ---- device buffers ----
-    int64_t max_chunk_bytes = 0;
-    for (int c = 0; c < nch; ++c) max_chunk_bytes = std::max(max_chunk_bytes, chunk_bytes(bound[c], bound[c + 1]));
-    for (int b = 0; b < std::min(nch, kRowBufs); ++b) CU_TRY(D.rows[b].need((size_t)max_chunk_bytes));
+    for (int g = 0; g < ng; ++g) {
+        int64_t biggest = 0;
+        int n_items = 0;
+        for (int c = 0; c < nch; ++c)
+            if (items[c].g == g) { biggest = std::max(biggest, item_bytes(g, items[c].lo, items[c].hi)); ++n_items; }
+        for (int b = 0; b < std::min(n_items, kRowBufs); ++b) CU_TRY(D.rows[g][b].need((size_t)biggest));
+    }
     CU_TRY(D.words.need(total_words * 4 + 16));
     CU_TRY(D.h_words.need(total_words * 4 + 16));
     CU_TRY(D.state.need((size_t)na * 16));
@@ -704,7 +746,7 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     std::vector<ChunkInfo> ci(nch);
     size_t n_desc = 0;
     for (int c = 0; c < nch; ++c)
-        for (int a = 0; a < na; ++a) n_desc += streams[act[a]].n > bound[c] ? 1 : 0;
+        for (int a = grp_begin[items[c].g]; a < grp_begin[items[c].g + 1]; ++a) n_desc += streams[act[a]].n > items[c].lo ? 1 : 0;
     const size_t rows_desc_bytes = (n_desc * sizeof(RowsDesc) + 15) / 16 * 16;
     CU_TRY(D.h_desc.need(rows_desc_bytes + n_desc * sizeof(PopDesc)));
     CU_TRY(D.desc.need(rows_desc_bytes + n_desc * sizeof(PopDesc)));
@@ -729,11 +771,11 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
             ci[c].first = (int)k;
             int blocks = 0;
             size_t roff = 0;
-            char* rbase = static_cast<char*>(D.rows[c % kRowBufs].p);
-            for (int a = 0; a < na; ++a) {
+            char* rbase = static_cast<char*>(D.rows[items[c].g][items[c].k % kRowBufs].p);
+            for (int a = grp_begin[items[c].g]; a < grp_begin[items[c].g + 1]; ++a) {
                 const flashgmm_stream& s = streams[act[a]];
-                if (s.n <= bound[c]) continue;
-                const int64_t c0 = bound[c], cnt = std::min(s.n, bound[c + 1]) - c0;
+                if (s.n <= items[c].lo) continue;
+                const int64_t c0 = items[c].lo, cnt = std::min(s.n, items[c].hi) - c0;
                 RowsDesc& r = h_rd[k];
                 r.p = stream_view(a, c0);
                 r.table32 = reinterpret_cast<uint32_t*>(rbase + roff);
@@ -762,10 +804,10 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     // (each parameter exactly once, 128-byte coalesced requests, thousands of warps in flight).
     auto upload_chunk = [&](int c) -> int {
         if (mem == FLASHGMM_MEM_HOST) {
-            for (int a = 0; a < na; ++a) {
+            for (int a = grp_begin[items[c].g]; a < grp_begin[items[c].g + 1]; ++a) {
                 const flashgmm_stream& s = streams[act[a]];
-                if (s.n <= bound[c] || is_zc[a]) continue;
-                const int64_t c0 = bound[c], cnt = std::min(s.n, bound[c + 1]) - c0;
+                if (s.n <= items[c].lo || is_zc[a]) continue;
+                const int64_t c0 = items[c].lo, cnt = std::min(s.n, items[c].hi) - c0;
                 float* b = d_par + par_off[a];
                 const float* src[3] = {s.scales, s.means, s.weights};
                 for (int t = 0; t < 3; ++t) {
@@ -786,7 +828,7 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
 
     auto launch_rows = [&](int c) -> int {
         CU_TRY(cudaStreamWaitEvent(D.st_rows, D.ev_up[c], 0));
-        if (c >= kRowBufs) CU_TRY(cudaStreamWaitEvent(D.st_rows, D.ev_pop[c - kRowBufs], 0));
+        if (items[c].ring_prev >= 0) CU_TRY(cudaStreamWaitEvent(D.st_rows, D.ev_pop[items[c].ring_prev], 0));
         if (prof) CU_TRY(cudaEventRecord(D.t0[2 * c], D.st_rows));
         CU_TRY(launch_gmm_cdf_rows_batched(d_rd + ci[c].first, ci[c].count, ci[c].blocks, S, max_row_words, lane_slots,
                                            mode, D.st_rows));
@@ -796,46 +838,66 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
         return FLASHGMM_OK;
     };
     auto launch_pop = [&](int c) -> int {
-        CU_TRY(cudaStreamWaitEvent(D.st_pop, D.ev_rows[c], 0));
-        if (c == 0) CU_TRY(cudaStreamWaitEvent(D.st_pop, D.ev_words, 0));
-        if (prof) CU_TRY(cudaEventRecord(D.t0[2 * c + 1], D.st_pop));
-        CU_TRY(launch_gmm_pop_rows(d_pd + ci[c].first, ci[c].count, lane_slots, mode, D.st_pop));
-        if (prof) CU_TRY(cudaEventRecord(D.t1[2 * c + 1], D.st_pop));
-        CU_TRY(cudaEventRecord(D.ev_pop[c], D.st_pop));
+        cudaStream_t sp = D.st_pop[items[c].g];
+        CU_TRY(cudaStreamWaitEvent(sp, D.ev_rows[c], 0));
+        if (items[c].lo == 0) CU_TRY(cudaStreamWaitEvent(sp, D.ev_words[items[c].g], 0));
+        if (prof) CU_TRY(cudaEventRecord(D.t0[2 * c + 1], sp));
+        CU_TRY(launch_gmm_pop_rows(d_pd + ci[c].first, ci[c].count, lane_slots, mode, sp));
+        if (prof) CU_TRY(cudaEventRecord(D.t1[2 * c + 1], sp));
+        CU_TRY(cudaEventRecord(D.ev_pop[c], sp));
+        if (items[c].hi >= streams[act[grp_begin[items[c].g]]].n) {
+            // the group's last item: its final states and (host callers) its symbols go home behind it
+            const int a0 = grp_begin[items[c].g], a1 = grp_begin[items[c].g + 1];
+            CU_TRY(cudaMemcpyAsync(static_cast<char*>(D.h_state.p) + 16 * (size_t)a0, static_cast<char*>(D.state.p) + 16 * (size_t)a0,
+                                   16 * (size_t)(a1 - a0), cudaMemcpyDeviceToHost, sp));
+            if (mem == FLASHGMM_MEM_HOST)
+                for (int a = a0; a < a1; ++a) {
+                    const flashgmm_stream& s = streams[act[a]];
+                    CU_TRY(cudaMemcpyAsync(s.symbols_out, d_out + out_off[a], (size_t)s.n * 4, cudaMemcpyDeviceToHost, sp));
+                }
+        }
         g_launches.fetch_add(1, std::memory_order_relaxed);
         return FLASHGMM_OK;
     };
 
     // The first chunk's rows launch goes out first, then the bitstreams (their own stream: pop(0)
     // must not wait behind parameter traffic), then the staging copies of pageable tensors; rows
-    // kernels are queued up to kRowBufs - 1 chunks ahead of the pop kernel.
+    // kernels run up to kRowBufs - 1 items ahead of their group's pop kernel.
     if (prof) CU_TRY(cudaEventRecord(D.t0[3 * nch], D.st_copy));
     if ((rc = upload_chunk(0))) return rc;
     if ((rc = launch_rows(0))) return rc;
     {
+        // group by group, the longest streams' words first: their pop is the critical path
         uint32_t* hw = static_cast<uint32_t*>(D.h_words.p);
-        for (int a = 0; a < na; ++a) {
-            const flashgmm_stream& s = streams[act[a]];
-            memcpy(hw + word_off[a], s.bytes, s.bytes_cap / 4 * 4);
+        for (int g = 0; g < ng; ++g) {
+            const int a0 = grp_begin[g], a1 = grp_begin[g + 1];
+            for (int a = a0; a < a1; ++a) {
+                const flashgmm_stream& s = streams[act[a]];
+                memcpy(hw + word_off[a], s.bytes, s.bytes_cap / 4 * 4);
+            }
+            const size_t w0 = word_off[a0], w1 = a1 < na ? word_off[a1] : total_words;
+            CU_TRY(cudaMemcpyAsync(static_cast<uint32_t*>(D.words.p) + w0, hw + w0, (w1 - w0) * 4, cudaMemcpyHostToDevice,
+                                   D.st_words));
+            CU_TRY(cudaEventRecord(D.ev_words[g], D.st_words));
         }
-        CU_TRY(cudaMemcpyAsync(D.words.p, D.h_words.p, total_words * 4, cudaMemcpyHostToDevice, D.st_words));
-        CU_TRY(cudaEventRecord(D.ev_words, D.st_words));
     }
     for (int c = 1; c < nch; ++c)
         if ((rc = upload_chunk(c))) return rc;
-    for (int c = 1; c < std::min(nch, kRowBufs - 1); ++c)
-        if ((rc = launch_rows(c))) return rc;
-    for (int c = 0; c < nch; ++c) {
-        if (c + kRowBufs - 1 < nch && (rc = launch_rows(c + kRowBufs - 1))) return rc;
-        if ((rc = launch_pop(c))) return rc;
-    }
-    CU_TRY(cudaMemcpyAsync(D.h_state.p, D.state.p, (size_t)na * 16, cudaMemcpyDeviceToHost, D.st_pop));
-    if (mem == FLASHGMM_MEM_HOST)
-        for (int a = 0; a < na; ++a) {
-            const flashgmm_stream& s = streams[act[a]];
-            CU_TRY(cudaMemcpyAsync(s.symbols_out, d_out + out_off[a], (size_t)s.n * 4, cudaMemcpyDeviceToHost, D.st_pop));
+    {
+        // enqueue order: a rows launch that reuses a buffer goes out after the pop launch that frees it
+        // (a wait on an event not yet recorded would be a no-op); otherwise pops trail rows by two items
+        int next_pop = 0;
+        for (int c = 1; c < nch; ++c) {
+            while (next_pop <= items[c].ring_prev)
+                if ((rc = launch_pop(next_pop++))) return rc;
+            if ((rc = launch_rows(c))) return rc;
+            while (next_pop + 2 <= c)
+                if ((rc = launch_pop(next_pop++))) return rc;
         }
-    CU_TRY(cudaStreamSynchronize(D.st_pop));
+        while (next_pop < nch)
+            if ((rc = launch_pop(next_pop++))) return rc;
+    }
+    for (int g = 0; g < ng; ++g) CU_TRY(cudaStreamSynchronize(D.st_pop[g]));
     CU_TRY(cudaStreamSynchronize(D.st_rows));
     CU_TRY(cudaStreamSynchronize(D.st_copy));
     CU_TRY(cudaStreamSynchronize(D.st_words));
@@ -848,8 +910,8 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
             cudaEventElapsedTime(&r1, D.t0[3 * nch], D.t1[2 * c]);
             cudaEventElapsedTime(&p0, D.t0[3 * nch], D.t0[2 * c + 1]);
             cudaEventElapsedTime(&p1, D.t0[3 * nch], D.t1[2 * c + 1]);
-            fprintf(stderr, "[flashgmm trace] chunk %d [%lld,%lld) streams %d: staged %.2f | rows %.2f-%.2f | pop %.2f-%.2f ms\n",
-                    c, (long long)bound[c], (long long)bound[c + 1], ci[c].count, up, r0, r1, p0, p1);
+            fprintf(stderr, "[flashgmm trace] item %d group %d [%lld,%lld) streams %d: staged %.2f | rows %.2f-%.2f | pop %.2f-%.2f ms\n",
+                    c, items[c].g, (long long)items[c].lo, (long long)items[c].hi, ci[c].count, up, r0, r1, p0, p1);
         }
     }
     if (prof) {
@@ -902,18 +964,22 @@ __attribute__((constructor)) static void flashgmm_more_hw_queues() {
 // batched startfreq kernel -> push kernel (one warp per stream) -> one D2H of the words.
 // Returns -1 when the batch is not eligible (pageable host tensors): the caller then takes
 // the worker-thread path.
-int encode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem) {
-    std::lock_guard<std::mutex> g(ctx->de_mu);
+// Two phases so that the caller's thread can queue the device part, push its share of the host
+// part, and only then wait: _begin queues everything (asynchronous), _finish waits and hands out
+// the streams. The caller holds ctx->de_mu across both.
+int encode_batch_device_begin(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem) {
     CU_TRY(cudaSetDevice(ctx->device));
     if (!ctx->de) ctx->de.reset(new DevEncode());
     DevEncode& E = *ctx->de;
     int rc = E.init();
     if (rc) return rc;
 
-    std::vector<int> act;
+    std::vector<int>& act = E.act;
+    act.clear();
+    E.worst = FLASHGMM_OK;
     std::vector<GmmParamsView> view(n_streams);
     std::vector<const int32_t*> sym(n_streams, nullptr);
-    int worst = FLASHGMM_OK;
+    int& worst = E.worst;
     for (int i = 0; i < n_streams; ++i) {
         flashgmm_stream& s = streams[i];
         s.bytes_len = 0;
@@ -931,7 +997,7 @@ int encode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
         act.push_back(i);
     }
     const int na = (int)act.size();
-    if (na == 0) return worst;
+    if (na == 0) return FLASHGMM_OK;
 
     std::vector<size_t> pk_off(na), sc_off(na);
     size_t pk_total = 0, sc_total = 0;
@@ -974,13 +1040,25 @@ int encode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     }
     CU_TRY(cudaMemcpyAsync(E.desc.p, E.h_desc.p, sf_bytes + (size_t)na * sizeof(PushDesc), cudaMemcpyHostToDevice, E.st));
     CU_TRY(cudaMemsetAsync(d_used, 0, 8, E.st));
-    const bool prof = g_prof_on.load(std::memory_order_relaxed) != 0;
+    const bool prof = E.prof = g_prof_on.load(std::memory_order_relaxed) != 0;
+    E.total_n = total_n;
     if (prof) CU_TRY(cudaEventRecord(E.t[0], E.st));
     CU_TRY(launch_gmm_startfreq_batched(static_cast<const SfDesc*>(E.desc.p), na, blocks, mode, E.st));
     if (prof) CU_TRY(cudaEventRecord(E.t[1], E.st));
     CU_TRY(launch_gmm_push(reinterpret_cast<const PushDesc*>(static_cast<char*>(E.desc.p) + sf_bytes), na,
                            static_cast<const PushRcp*>(E.rcp.p), static_cast<uint32_t*>(E.h_out.p), d_used, E.st));
     g_launches.fetch_add(2, std::memory_order_relaxed);
+    return FLASHGMM_OK;
+}
+
+int encode_batch_device_finish(flashgmm_ctx* ctx, flashgmm_stream* streams) {
+    DevEncode& E = *ctx->de;
+    const std::vector<int>& act = E.act;
+    const int na = (int)act.size();
+    int worst = E.worst;
+    if (na == 0) return worst;
+    const bool prof = E.prof;
+    const double total_n = E.total_n;
     CU_TRY(cudaStreamSynchronize(E.st));
     const uint32_t* hr = static_cast<const uint32_t*>(E.h_result.p);
     unsigned long long used_words = 0;
@@ -1133,7 +1211,7 @@ int flashgmm_ctx_create(int device, flashgmm_ctx** out) {
     long hw = (long)std::thread::hardware_concurrency();
     c->n_workers = (int)std::max<long>(1, env_long("FLASHGMM_WORKERS", std::min<long>(16, hw > 1 ? hw - 1 : 1)));
     c->pop_min_streams = (int)std::max<long>(1, env_long("FLASHGMM_POP_MIN_STREAMS", 4));
-    c->pop_rows_budget = std::max<long>(1 << 20, env_long("FLASHGMM_POP_ROWS_BYTES", 512l << 20));
+    c->pop_rows_budget = std::max<long>(1 << 20, env_long("FLASHGMM_POP_ROWS_BYTES", 256l << 20));
     {
         const char* pp = getenv("FLASHGMM_PUSH");            // host | device | (unset) auto
         c->push_policy = (pp && pp[0] == 'h') ? 1 : (pp && pp[0] == 'd') ? 2 : 0;
@@ -1232,23 +1310,27 @@ int flashgmm_gmm_encode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     std::vector<int> order;
     const int k_host = plan_push_split(ctx, streams, n_streams, &order);
     if (k_host >= n_streams) return run_batch(ctx, streams, n_streams, mode, mem, encode_stream);
-    // the n_streams - k_host shortest streams on the device (own thread, own CUDA stream) while the
+    // the n_streams - k_host shortest streams on the device (own CUDA stream) while the
     // k_host longest are pushed by the worker threads
     std::vector<flashgmm_stream> dev_part, host_part;
     for (int j = k_host; j < n_streams; ++j) dev_part.push_back(streams[order[j]]);
     for (int j = 0; j < k_host; ++j) host_part.push_back(streams[order[j]]);
-    int dev_rc = FLASHGMM_OK;
-    std::string dev_err;
-    std::thread dev_thread([&] {
-        dev_rc = encode_batch_device(ctx, dev_part.data(), (int)dev_part.size(), mode, mem);
-        if (dev_rc > 0) dev_err = g_err;
-    });
+    // the calling thread queues the device part (asynchronous), takes its share of the host part,
+    // then collects the device part
+    std::lock_guard<std::mutex> dg(ctx->de_mu);
+    int dev_rc = encode_batch_device_begin(ctx, dev_part.data(), (int)dev_part.size(), mode, mem);
+    const bool dev_queued = dev_rc == FLASHGMM_OK;
     int host_rc = host_part.empty() ? FLASHGMM_OK
                                     : run_batch(ctx, host_part.data(), (int)host_part.size(), mode, mem, encode_stream);
-    dev_thread.join();
-    if (dev_rc < 0)                                          // pageable host tensors: the workers take them too
+    if (dev_queued) {
+        const std::string host_err = host_rc ? g_err : std::string();
+        dev_rc = encode_batch_device_finish(ctx, dev_part.data());
+        if (host_rc) g_err = host_err;
+    } else if (dev_rc < 0) {                                 // pageable host tensors: the workers take them too
         dev_rc = run_batch(ctx, dev_part.data(), (int)dev_part.size(), mode, mem, encode_stream);
-    else if (dev_rc > 0) g_err = dev_err;
+    } else if (ctx->de && ctx->de->st) {
+        cudaStreamSynchronize(ctx->de->st);                  // a failed begin may have queued part of its work
+    }
     for (int j = 0; j < k_host; ++j) streams[order[j]] = host_part[j];
     for (int j = k_host; j < n_streams; ++j) streams[order[j]] = dev_part[j - k_host];
     return host_rc ? host_rc : dev_rc;
