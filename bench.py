@@ -38,9 +38,10 @@ ELIC_GROUPS = (16, 16, 32, 64, 192)          # elic_gmm.py:92-93
 LATENT_HW = (32, 48)                         # 512x768 / 16
 N_SETS = 2                                   # rotating batches of images (each batch > 126 MB L2 for B >= 5)
 # (dram__bytes_read.sum + dram__bytes_write.sum) / symbols of the captured launch, from the committed
-# ncu --set full captures (profiles/r01_s13_ncu_*.csv); multiplied by the symbols per launch of this
-# run to give `traffic` per launch. None until a capture of the current kernel exists.
-NCU_DRAM_BYTES_PER_SYMBOL = {"gmm_startfreq": 52.6, "gmm_cdf_rows": 261.6, "gmm_pop_rows": 367.8, "gmm_push": None}
+# ncu --set full captures (profiles/r01_s20_ncu_full_*.csv: batched startfreq 4.72 M symbols, rows
+# 786 432, pop 589 824, push 4.72 M); multiplied by the symbols per launch of this run to give
+# `traffic` per launch.
+NCU_DRAM_BYTES_PER_SYMBOL = {"gmm_startfreq": 55.3, "gmm_cdf_rows": 245.5, "gmm_pop_rows": 373.6, "gmm_push": 4.2}
 ALGO_BYTES_PER_SYMBOL = {"gmm_startfreq": 56.0, "gmm_cdf_rows": 48.0 + 272.0, "gmm_pop_rows": 272.0 + 4.0, "gmm_push": 4.0 + 8.0 * 0.14}
 
 
@@ -289,7 +290,7 @@ def run_b200(args):
         "gmm_pop_rows": "latency-bound by construction: the rANS state recurrence is serial per stream, one warp per "
                         "stream, ~115 cycles per symbol; HBM fraction is not the figure of merit, ns/symbol/stream is",
         "gmm_push": "latency-bound by construction: the rANS state recurrence is serial per stream, one warp per "
-                    "stream, ~170 cycles per symbol; runs beside the host worker threads on the shorter streams",
+                    "stream, ~95 cycles per symbol; runs beside the host worker threads on the shorter streams",
     }
 
     def roof(name):
@@ -319,8 +320,9 @@ def run_b200(args):
                          "(one batch alone exceeds the 126 MB L2)",
                    "bits_per_symbol": round(bits, 3), "search_radius": radii[0][0][-1],
                    "decode": "device-resident (rows kernel -> pop kernel, one warp per stream)",
-                   "encode": "startfreq kernel -> serial push: the longest streams on host worker threads, the rest on the "
-                             "device (push kernel, one warp per stream), split by a cost model (FLASHGMM_PUSH)",
+                   "encode": "batched startfreq launches -> serial push: the longest streams on host worker threads (records "
+                             "come down wave by wave), the rest on the device (push kernel, one warp per stream), "
+                             "split by a cost model (FLASHGMM_PUSH)",
                    "host_workers": int(os.environ.get("FLASHGMM_WORKERS", "0")) or min(16, max(1, (os.cpu_count() or 2) - 1)),
                    "host_cores": os.cpu_count()},
         "encode_ms_per_image": round(1e3 * enc_t / B, 4), "decode_ms_per_image": round(1e3 * dec_t / B, 4),

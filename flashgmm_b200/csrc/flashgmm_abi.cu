@@ -10,6 +10,7 @@
 //           the host pops chunk c while c+1, c+2 are in flight.
 // Batch calls spread independent streams over the ctx's lanes (one worker thread each).
 #include <atomic>
+#include <chrono>
 #include <algorithm>
 #include <condition_variable>
 #include <cstdarg>
@@ -251,6 +252,7 @@ struct DevDecode {
 struct DevEncode {
     cudaStream_t st = nullptr;
     cudaEvent_t t[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_sf = nullptr;          // the device part's CDF pass is done (its inputs have crossed PCIe)
     DevBuf packed, scratch, desc, rcp, result;
     PinBuf h_desc, h_result, h_out;
     bool rcp_ready = false;
@@ -263,14 +265,58 @@ struct DevEncode {
         if (st) return FLASHGMM_OK;
         CU_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
         for (auto& e : t) CU_TRY(cudaEventCreate(&e));
+        CU_TRY(cudaEventCreateWithFlags(&ev_sf, cudaEventDisableTiming));
         return FLASHGMM_OK;
     }
     void destroy() {
         if (st) cudaStreamDestroy(st);
         for (auto& e : t) if (e) { cudaEventDestroy(e); e = nullptr; }
+        if (ev_sf) { cudaEventDestroy(ev_sf); ev_sf = nullptr; }
         st = nullptr; rcp_ready = false;
         packed.release(); scratch.release(); desc.release(); rcp.release(); result.release();
         h_desc.release(); h_result.release(); h_out.release();
+    }
+};
+
+// Buffers of the batched host-push path (one startfreq launch per wave of all streams, records
+// written straight into page-locked host memory, worker threads push them as the waves land).
+struct HostWaves {
+    cudaStream_t st = nullptr, st_down = nullptr;    // CDF kernels | copies of their records to the host
+    std::vector<cudaEvent_t> ev, evk, t0, t1;        // per wave: records are on the host | kernel done
+    DevBuf desc, d_packed;
+    PinBuf h_desc, h_packed;
+    // one word buffer per stream, reused across calls; each on its own cache lines (workers on
+    // neighbouring streams would otherwise fight over the line holding the write cursors)
+    struct alignas(128) PaddedBuffer { BackBuffer b; };
+    std::vector<std::unique_ptr<PaddedBuffer>> bb;
+    int init() {
+        if (st) return FLASHGMM_OK;
+        CU_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        CU_TRY(cudaStreamCreateWithFlags(&st_down, cudaStreamNonBlocking));
+        return FLASHGMM_OK;
+    }
+    int need_events(size_t n, bool timers) {
+        while (ev.size() < n) {
+            cudaEvent_t e, k;
+            CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            CU_TRY(cudaEventCreateWithFlags(&k, cudaEventDisableTiming));
+            ev.push_back(e); evk.push_back(k);
+        }
+        while (timers && t0.size() < n) {
+            cudaEvent_t a, b;
+            CU_TRY(cudaEventCreate(&a));
+            CU_TRY(cudaEventCreate(&b));
+            t0.push_back(a); t1.push_back(b);
+        }
+        return FLASHGMM_OK;
+    }
+    void destroy() {
+        for (auto v : {&ev, &evk, &t0, &t1}) { for (auto e : *v) cudaEventDestroy(e); v->clear(); }
+        if (st) cudaStreamDestroy(st);
+        if (st_down) cudaStreamDestroy(st_down);
+        st = st_down = nullptr;
+        desc.release(); d_packed.release(); h_desc.release(); h_packed.release();
+        bb.clear();
     }
 };
 
@@ -293,9 +339,10 @@ struct flashgmm_ctx {
     int64_t pop_rows_budget = 256ll << 20;
     // device-resident encode (startfreq kernel -> push kernel): chosen per call by a cost model
     std::unique_ptr<DevEncode> de;
+    std::unique_ptr<HostWaves> hw;
     std::mutex de_mu;                 // the device encode path owns its buffers and stream: it runs beside the workers
     int push_policy = 0;              // 0 auto, 1 always host workers, 2 always device
-    double push_host_ns = 7.5, push_dev_ns = 87.0;   // per symbol: one host worker / one device warp (measured, B200 box)
+    double push_host_ns = 4.5, push_dev_ns = 46.0;   // per symbol: one host worker / one device warp (measured, B200 box)
 };
 
 namespace {
@@ -1032,7 +1079,7 @@ int encode_batch_device_begin(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     double total_n = 0;
     for (int a = 0; a < na; ++a) {
         const flashgmm_stream& s = streams[act[a]];
-        h_sf[a] = SfDesc{view[act[a]], sym[act[a]], d_packed + pk_off[a], (int32_t)s.n, blocks};
+        h_sf[a] = SfDesc{view[act[a]], sym[act[a]], d_packed + pk_off[a], (int32_t)s.n, blocks, nullptr};
         blocks += (int)((s.n + 127) / 128);
         h_pd[a] = PushDesc{d_packed + pk_off[a], sym[act[a]], static_cast<uint32_t*>(E.scratch.p) + sc_off[a],
                            (uint32_t)(s.bytes_cap / 4), (int32_t)s.n, d_result + 8 * (size_t)a};
@@ -1045,6 +1092,7 @@ int encode_batch_device_begin(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     if (prof) CU_TRY(cudaEventRecord(E.t[0], E.st));
     CU_TRY(launch_gmm_startfreq_batched(static_cast<const SfDesc*>(E.desc.p), na, blocks, mode, E.st));
     if (prof) CU_TRY(cudaEventRecord(E.t[1], E.st));
+    CU_TRY(cudaEventRecord(E.ev_sf, E.st));
     CU_TRY(launch_gmm_push(reinterpret_cast<const PushDesc*>(static_cast<char*>(E.desc.p) + sf_bytes), na,
                            static_cast<const PushRcp*>(E.rcp.p), static_cast<uint32_t*>(E.h_out.p), d_used, E.st));
     g_launches.fetch_add(2, std::memory_order_relaxed);
@@ -1091,8 +1139,8 @@ int encode_batch_device_finish(flashgmm_ctx* ctx, flashgmm_stream* streams) {
     return worst;
 }
 
-// Host workers or device warps for the serial push? A host worker does ~7.5 ns per symbol, a
-// device warp ~87 ns but every stream has its own. Streams are sorted by length; the `k` longest go
+// Host workers or device warps for the serial push? A host worker does ~4.5 ns per symbol (waves path,
+// tail effects included), a device warp ~46 ns but every stream has its own. Streams are sorted by length; the `k` longest go
 // to the worker threads, the rest to the device, both at once: k minimises the later finish.
 // (One free box: the long streams stay on the host, the many short ones go to the GPU. Several
 // ranks sharing few cores: most or all of the batch goes to the GPU.)
@@ -1155,6 +1203,239 @@ int run_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mo
     ctx->pool->run(work, nw);
     int worst = FLASHGMM_OK;
     for (int i = 0; i < n_streams; ++i) if (streams[i].status) worst = streams[i].status;
+    if (worst) for (auto& e : errs) if (!e.empty()) { g_err = e; break; }
+    return worst;
+}
+
+// ---------------- encode a batch: batched CDF waves on the device, push on the workers ----------------
+// The worker-thread path of run_batch(encode_stream) launches one small kernel and one copy per
+// stream chunk and waits for each: with page-locked host inputs (kernels read them over PCIe) the
+// link idles whenever the workers are busy pushing. Here ONE stream of batched startfreq launches
+// covers every stream of the batch wave by wave -- a wave is a symbol range counted from the END of
+// each stream, because the encoder walks backwards -- and writes the packed records straight into
+// page-locked host memory; the workers take (wave, stream) tasks in wave-major order and push each
+// as soon as its wave's event has fired and the stream's previous wave is done. PCIe (or the FP32
+// pipe) never waits for a push, and a worker makes no CUDA call per task beyond the event wait.
+// `gate` (optional): an event the first wave waits for (the device part of a split batch goes first).
+// Returns -1 when the batch is not eligible (pageable host tensors), before touching anything.
+int encode_batch_waves(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem, cudaEvent_t gate) {
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CU_TRY(cudaSetDevice(ctx->device));
+    if (!ctx->hw) ctx->hw.reset(new HostWaves());
+    HostWaves& H = *ctx->hw;
+    int rc = H.init();
+    if (rc) return rc;
+
+    std::vector<int> act;
+    std::vector<GmmParamsView> view(n_streams);
+    std::vector<const int32_t*> sym(n_streams, nullptr);
+    int worst = FLASHGMM_OK;
+    if (mem == FLASHGMM_MEM_HOST)                          // eligibility first: nothing is modified on -1
+        for (int i = 0; i < n_streams; ++i) {
+            const flashgmm_stream& s = streams[i];
+            GmmParamsView v{};
+            const int32_t* sp = nullptr;
+            if (s.n > 0 && s.scales && s.means && s.weights && s.symbols && !zero_copy_view(s, true, &v, &sp)) return -1;
+        }
+    int64_t max_n = 0;
+    for (int i = 0; i < n_streams; ++i) {
+        flashgmm_stream& s = streams[i];
+        s.bytes_len = 0;
+        s.status = check_gmm_args(s.scales, s.means, s.weights, s.n, s.stride_n, s.stride_k, mode, mem);
+        if (!s.status && s.n > 0 && !s.symbols) s.status = fail(FLASHGMM_EINVAL, "null symbols");
+        if (!s.status && !s.bytes && s.bytes_cap) s.status = fail(FLASHGMM_EINVAL, "null output buffer");
+        if (!s.status && s.n > INT32_MAX / 2) s.status = fail(FLASHGMM_EINVAL, "stream too long for one call");
+        if (s.status) { worst = s.status; continue; }
+        if (mem == FLASHGMM_MEM_DEVICE) { view[i] = device_view(s, 0); sym[i] = s.symbols; }
+        else if (s.n > 0) zero_copy_view(s, true, &view[i], &sym[i]);
+        act.push_back(i);
+        max_n = std::max(max_n, s.n);
+    }
+    const int na = (int)act.size();
+    if (na == 0) return worst;
+
+    // ---- waves (distances from the end of each stream) and tasks ----
+    std::vector<int64_t> wb{0};
+    for (int64_t step = 8192; wb.back() < max_n; step = 16384) wb.push_back(wb.back() + step);
+    const int nw_waves = (int)wb.size() - 1;
+    struct Task { int w, a; int64_t lo, hi; };
+    std::vector<Task> tasks;
+    std::vector<size_t> t_off;                               // wave-major record layout: one copy per wave
+    size_t pk_total = 0;
+    std::vector<int> wave_first(nw_waves + 1, 0), wave_blocks(nw_waves, 0), last_wave(na, -1);
+    for (int w = 0; w < nw_waves; ++w) {
+        wave_first[w] = (int)tasks.size();
+        for (int a = 0; a < na; ++a) {
+            const int64_t n = streams[act[a]].n;
+            if (n <= wb[w]) continue;
+            tasks.push_back(Task{w, a, n - std::min(n, wb[w + 1]), n - wb[w]});
+            t_off.push_back(pk_total);
+            pk_total += (size_t)round_up(tasks.back().hi - tasks.back().lo, 32) + 32;   // 128-byte aligned slots; the word after the records is the bypass flag
+            last_wave[a] = w;
+        }
+    }
+    wave_first[nw_waves] = (int)tasks.size();
+    const int nt = (int)tasks.size();
+
+    const bool prof = g_prof_on.load(std::memory_order_relaxed) != 0;
+    if ((rc = H.need_events((size_t)std::max(1, nw_waves), prof))) return rc;
+    t_off.push_back(pk_total);
+    CU_TRY(H.h_packed.need(pk_total * 4 + 16));
+    CU_TRY(H.d_packed.need(pk_total * 4 + 16));
+    CU_TRY(H.h_desc.need((size_t)std::max(1, nt) * sizeof(SfDesc)));
+    CU_TRY(H.desc.need((size_t)std::max(1, nt) * sizeof(SfDesc)));
+    // records go to device memory and come down with one copy per wave (a kernel writing 4-byte
+    // records straight into page-locked host memory managed ~4 GB/s)
+    uint32_t* packed = static_cast<uint32_t*>(H.h_packed.p);
+    uint32_t* d_packed = static_cast<uint32_t*>(H.d_packed.p);
+    SfDesc* h_sf = static_cast<SfDesc*>(H.h_desc.p);
+    for (int w = 0; w < nw_waves; ++w) {
+        int blocks = 0;
+        for (int t = wave_first[w]; t < wave_first[w + 1]; ++t) {
+            const Task& k = tasks[t];
+            const flashgmm_stream& s = streams[act[k.a]];
+            const GmmParamsView& v = view[act[k.a]];
+            h_sf[t] = SfDesc{GmmParamsView{v.scales + k.lo * s.stride_n, v.means + k.lo * s.stride_n,
+                                           v.weights + k.lo * s.stride_n, s.stride_n, s.stride_k},
+                             sym[act[k.a]] + k.lo, d_packed + t_off[t], (int32_t)(k.hi - k.lo), blocks,
+                             d_packed + t_off[t] + round_up(k.hi - k.lo, 32)};
+            blocks += (int)((k.hi - k.lo + 127) / 128);
+        }
+        wave_blocks[w] = blocks;
+    }
+    CU_TRY(cudaMemcpyAsync(H.desc.p, H.h_desc.p, (size_t)nt * sizeof(SfDesc), cudaMemcpyHostToDevice, H.st));
+    CU_TRY(cudaMemsetAsync(d_packed, 0, pk_total * 4, H.st));      // clears the bypass flags (HBM speed: microseconds)
+    if (gate) CU_TRY(cudaStreamWaitEvent(H.st, gate, 0));
+    for (int w = 0; w < nw_waves; ++w) {
+        if (prof) CU_TRY(cudaEventRecord(H.t0[w], H.st));
+        CU_TRY(launch_gmm_startfreq_batched(static_cast<const SfDesc*>(H.desc.p) + wave_first[w],
+                                            wave_first[w + 1] - wave_first[w], wave_blocks[w], mode, H.st));
+        if (prof) CU_TRY(cudaEventRecord(H.t1[w], H.st));
+        CU_TRY(cudaEventRecord(H.evk[w], H.st));
+        CU_TRY(cudaStreamWaitEvent(H.st_down, H.evk[w], 0));
+        const size_t w0 = t_off[wave_first[w]], w1 = t_off[wave_first[w + 1]];
+        CU_TRY(cudaMemcpyAsync(packed + w0, d_packed + w0, (w1 - w0) * 4, cudaMemcpyDeviceToHost, H.st_down));
+        CU_TRY(cudaEventRecord(H.ev[w], H.st_down));
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+    }
+
+    static const bool wtrace = env_long("FLASHGMM_TRACE", 0) != 0;
+    const auto tr0 = std::chrono::steady_clock::now();
+    auto ms_since = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tr0).count(); };
+    std::vector<double> t_landed(std::max(1, nw_waves), 0.0);
+    std::vector<double> acc(4 * 64, 0.0);                     // trace: per worker ms in event wait / order wait / scan / push
+    // ---- workers ----
+    while ((int)H.bb.size() < na) H.bb.emplace_back(new HostWaves::PaddedBuffer());
+    std::vector<RansEncoder64> enc(na);
+    for (int a = 0; a < na; ++a) {
+        H.bb[a]->b.reset((size_t)(streams[act[a]].n * 9 / 16) + 64);
+        enc[a].init(&H.bb[a]->b);
+    }
+    std::unique_ptr<std::atomic<int>[]> done(new std::atomic<int>[na]);
+    for (int a = 0; a < na; ++a) done[a].store(0, std::memory_order_relaxed);
+    std::unique_ptr<std::atomic<int>[]> landed(new std::atomic<int>[std::max(1, nw_waves)]);
+    for (int w = 0; w < nw_waves; ++w) landed[w].store(0, std::memory_order_relaxed);
+    auto finish_stream = [&](int a) {
+        flashgmm_stream& s = streams[act[a]];
+        enc[a].flush();
+        s.bytes_len = H.bb[a]->b.bytes();
+        if (s.bytes_len > s.bytes_cap)
+            s.status = fail(FLASHGMM_ENOSPC, "output buffer too small: need %zu bytes, have %zu", s.bytes_len, s.bytes_cap);
+        else
+            memcpy(s.bytes, H.bb[a]->b.data(), s.bytes_len);
+    };
+    for (int a = 0; a < na; ++a) if (last_wave[a] < 0) finish_stream(a);     // empty streams: flush only
+    if (!ctx->pool) ctx->pool.reset(new Pool(ctx->n_workers));
+    const int nw = std::max(1, std::min(ctx->n_workers, nt));
+    std::atomic<int> next{0};
+    std::vector<std::string> errs(nw);
+    std::vector<int> cuda_fail(nw, 0);
+    std::function<void(int)> work = [&](int wi) {
+        cudaSetDevice(ctx->device);
+        std::vector<int32_t> tmp;
+        for (;;) {
+            const int t = next.fetch_add(1);
+            if (t >= nt) break;
+            const Task& k = tasks[t];
+            flashgmm_stream& s = streams[act[k.a]];
+            const double c0 = wtrace ? ms_since() : 0.0;
+            if (!landed[k.w].load(std::memory_order_acquire)) {
+                if (cudaEventSynchronize(H.ev[k.w]) != cudaSuccess) cuda_fail[wi] = 1;
+                if (wtrace && t_landed[k.w] == 0.0) t_landed[k.w] = ms_since();
+                landed[k.w].store(1, std::memory_order_release);
+            }
+            const double cA = wtrace ? ms_since() : 0.0;
+            // the stream's earlier waves (taken by other workers before this task was) must be pushed first
+            for (int spin = 0; done[k.a].load(std::memory_order_acquire) != k.w; ++spin)
+                if (spin > 64) std::this_thread::yield();
+            const double c1 = wtrace ? ms_since() : 0.0;
+            const int64_t cnt = k.hi - k.lo;
+            const uint32_t* pk = packed + t_off[t];
+            const int32_t* sym_h = nullptr;
+            if (mem == FLASHGMM_MEM_HOST) {
+                sym_h = s.symbols + k.lo;
+            } else {
+                // bypass records (rare) need the symbol's value: the kernel left the first few
+                // (index, value) pairs behind the records; more than that, fetch the range
+                const uint32_t* tail = pk + round_up(cnt, 32);
+                if (tail[0] > (uint32_t)kSfBypassSlots) {
+                    tmp.resize((size_t)cnt);
+                    if (cudaMemcpy(tmp.data(), s.symbols + k.lo, (size_t)cnt * 4, cudaMemcpyDeviceToHost) != cudaSuccess)
+                        cuda_fail[wi] = 1;
+                    sym_h = tmp.data();
+                }
+            }
+            const double c2 = wtrace ? ms_since() : 0.0;
+            if (!cuda_fail[wi]) {
+                RansEncoder64 e = enc[k.a];                  // state on this worker's stack while it runs:
+                if (sym_h != nullptr) {                      // neighbouring streams' states share cache lines
+                    e.push_chunk_reverse(pk, sym_h, cnt);
+                } else {
+                    const uint32_t* tail = pk + round_up(cnt, 32);
+                    e.push_chunk_reverse_with(pk, cnt, [tail](int64_t i) {
+                        for (uint32_t j = 0; j < tail[0]; ++j)
+                            if (tail[1 + 2 * j] == (uint32_t)i) return (int32_t)tail[2 + 2 * j];
+                        return 0;
+                    });
+                }
+                enc[k.a] = e;
+            }
+            if (wtrace) {
+                const double c3 = ms_since();
+                acc[4 * wi] += cA - c0; acc[4 * wi + 1] += c1 - cA; acc[4 * wi + 2] += c2 - c1; acc[4 * wi + 3] += c3 - c2;
+            }
+            if (k.w == last_wave[k.a]) {
+                finish_stream(k.a);
+                if (s.status) errs[wi] = g_err;
+            }
+            done[k.a].store(k.w + 1, std::memory_order_release);
+        }
+    };
+    const double t_setup = ms_since();
+    ctx->pool->run(work, nw);
+    if (wtrace) {
+        fprintf(stderr, "[flashgmm trace] encode waves: %d streams, %d tasks, %d workers; workers start %.2f ms, done %.2f ms; waves landed at",
+                na, nt, nw, t_setup, ms_since());
+        for (int w = 0; w < nw_waves; ++w) fprintf(stderr, " %.2f", t_landed[w]);
+        fprintf(stderr, "\n[flashgmm trace]   per worker ms (event wait / order wait / scan / push):");
+        for (int i = 0; i < std::min(nw, 64); ++i) fprintf(stderr, " %.2f/%.2f/%.2f/%.2f", acc[4 * i], acc[4 * i + 1], acc[4 * i + 2], acc[4 * i + 3]);
+        fprintf(stderr, "\n");
+    }
+    CU_TRY(cudaStreamSynchronize(H.st));
+    CU_TRY(cudaStreamSynchronize(H.st_down));
+    for (int f : cuda_fail) if (f) return fail(FLASHGMM_ECUDA, "CUDA error in the batched encode path: %s", cudaGetErrorString(cudaGetLastError()));
+    if (prof) {
+        std::lock_guard<std::mutex> pg(g_prof_mu);
+        for (int w = 0; w < nw_waves; ++w) {
+            float ms = 0;
+            double n_w = 0;
+            for (int t = wave_first[w]; t < wave_first[w + 1]; ++t) n_w += (double)(tasks[t].hi - tasks[t].lo);
+            if (cudaEventElapsedTime(&ms, H.t0[w], H.t1[w]) == cudaSuccess) {
+                g_prof_ms[PROF_STARTFREQ] += ms; g_prof_bytes[PROF_STARTFREQ] += 56.0 * n_w; g_prof_launches[PROF_STARTFREQ] += 1;
+            }
+        }
+    }
+    for (int a = 0; a < na; ++a) if (streams[act[a]].status) worst = streams[act[a]].status;
     if (worst) for (auto& e : errs) if (!e.empty()) { g_err = e; break; }
     return worst;
 }
@@ -1228,6 +1509,7 @@ void flashgmm_ctx_destroy(flashgmm_ctx* ctx) {
     for (auto& l : ctx->lanes) l->destroy();
     if (ctx->dd) ctx->dd->destroy();
     if (ctx->de) ctx->de->destroy();
+    if (ctx->hw) ctx->hw->destroy();
     ctx->il_scratch.release(); ctx->il_segw.release(); ctx->il_out.release(); ctx->il_err.release();
     ctx->il_host.release();
     delete ctx;
@@ -1309,7 +1591,17 @@ int flashgmm_gmm_encode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     if (n_streams < 0 || (n_streams > 0 && !streams)) return fail(FLASHGMM_EINVAL, "bad stream array");
     std::vector<int> order;
     const int k_host = plan_push_split(ctx, streams, n_streams, &order);
-    if (k_host >= n_streams) return run_batch(ctx, streams, n_streams, mode, mem, encode_stream);
+    static const bool waves = env_long("FLASHGMM_ENC_WAVES", 1) != 0;
+    // host part: batched CDF waves + worker pushes; falls back to one kernel per stream chunk for
+    // pageable host tensors (-1) or when switched off
+    auto host_encode = [&](flashgmm_stream* part, int n_part, cudaEvent_t gate) -> int {
+        if (waves && n_part >= 2) {
+            const int rc = encode_batch_waves(ctx, part, n_part, mode, mem, gate);
+            if (rc != -1) return rc;
+        }
+        return run_batch(ctx, part, n_part, mode, mem, encode_stream);
+    };
+    if (k_host >= n_streams) return host_encode(streams, n_streams, nullptr);
     // the n_streams - k_host shortest streams on the device (own CUDA stream) while the
     // k_host longest are pushed by the worker threads
     std::vector<flashgmm_stream> dev_part, host_part;
@@ -1320,14 +1612,16 @@ int flashgmm_gmm_encode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     std::lock_guard<std::mutex> dg(ctx->de_mu);
     int dev_rc = encode_batch_device_begin(ctx, dev_part.data(), (int)dev_part.size(), mode, mem);
     const bool dev_queued = dev_rc == FLASHGMM_OK;
-    int host_rc = host_part.empty() ? FLASHGMM_OK
-                                    : run_batch(ctx, host_part.data(), (int)host_part.size(), mode, mem, encode_stream);
+    // host inputs: the device part's parameters cross PCIe first (its push then runs while the host
+    // part's cross), instead of both halving the link
+    cudaEvent_t gate = (dev_queued && mem == FLASHGMM_MEM_HOST && !ctx->de->act.empty()) ? ctx->de->ev_sf : nullptr;
+    int host_rc = host_part.empty() ? FLASHGMM_OK : host_encode(host_part.data(), (int)host_part.size(), gate);
     if (dev_queued) {
         const std::string host_err = host_rc ? g_err : std::string();
         dev_rc = encode_batch_device_finish(ctx, dev_part.data());
         if (host_rc) g_err = host_err;
     } else if (dev_rc < 0) {                                 // pageable host tensors: the workers take them too
-        dev_rc = run_batch(ctx, dev_part.data(), (int)dev_part.size(), mode, mem, encode_stream);
+        dev_rc = host_encode(dev_part.data(), (int)dev_part.size(), nullptr);
     } else if (ctx->de && ctx->de->st) {
         cudaStreamSynchronize(ctx->de->st);                  // a failed begin may have queued part of its work
     }

@@ -362,7 +362,13 @@ gmm_startfreq_batched_kernel(const SfDesc* __restrict__ descs, int n_desc) {
     if (i >= d.n) return;
     float mu[4], sg[4], w[4];
     load_generic(d.p, i, mu, sg, w);
-    d.packed[i] = gmm_startfreq1<MODE>(__ldg(d.sym + i), mu, sg, w);
+    const int32_t v = __ldg(d.sym + i);
+    const uint32_t r = gmm_startfreq1<MODE>(v, mu, sg, w);
+    d.packed[i] = r;
+    if (r == FGMM_PACK_BYPASS && d.flag != nullptr) {        // rare: hand the pusher the value it will need
+        const uint32_t j = atomicAdd(d.flag, 1u);
+        if (j < (uint32_t)kSfBypassSlots) { d.flag[1 + 2 * j] = (uint32_t)i; d.flag[2 + 2 * j] = (uint32_t)v; }
+    }
 }
 
 cudaError_t launch_gmm_startfreq_batched(const SfDesc* descs_d, int n_desc, int total_blocks, int mode, cudaStream_t st) {
@@ -406,22 +412,8 @@ cudaError_t launch_rows_mode(const GmmParamsView& p, int64_t n, int R, uint16_t*
 cudaError_t launch_gmm_cdf_rows_batched(const RowsDesc* descs_d, int n_desc, int total_blocks, int S,
                                         int max_row_words, int lane_slots, int mode, cudaStream_t st) {
     if (n_desc <= 0 || total_blocks <= 0) return cudaSuccess;
-    size_t smem = (size_t)S * (12 + max_row_words + 2) * 4;    // + bad flag + window base per symbol
+    const size_t smem = (size_t)S * (12 + max_row_words + 2) * 4;    // + bad flag + window base per symbol
     if (smem > 48 * 1024) return cudaErrorInvalidValue;      // callers size S for the widest row
-    // FLASHGMM_ROWS_CTAS_PER_SM=k caps the rows kernel's residency (by asking for more shared memory
-    // than it uses): the pop warps it shares the SMs with then find free issue slots more often.
-    static const int ctas_per_sm = [] { const char* e = getenv("FLASHGMM_ROWS_CTAS_PER_SM"); return e ? atoi(e) : 0; }();
-    if (ctas_per_sm > 0) {
-        static const bool raised = [] {
-            const int big = 226 * 1024;
-            cudaFuncSetAttribute(gmm_cdf_rows_batched_kernel<MODE_AS>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
-            cudaFuncSetAttribute(gmm_cdf_rows_batched_kernel<MODE_LOGISTIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
-            cudaFuncSetAttribute(gmm_cdf_rows_batched_kernel<MODE_POLYA>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
-            return true;
-        }();
-        (void)raised;
-        smem = std::max(smem, (size_t)(228 * 1024 / ctas_per_sm - 1536));
-    }
     switch (mode) {
     case MODE_AS: gmm_cdf_rows_batched_kernel<MODE_AS><<<total_blocks, kRowThreads, smem, st>>>(descs_d, n_desc, S, lane_slots); break;
     case MODE_LOGISTIC: gmm_cdf_rows_batched_kernel<MODE_LOGISTIC><<<total_blocks, kRowThreads, smem, st>>>(descs_d, n_desc, S, lane_slots); break;

@@ -69,12 +69,15 @@ cudaError_t launch_gmm_cdf_rows_batched(const RowsDesc* descs_d, int n_desc, int
 cudaError_t launch_gmm_pop_rows(const PopDesc* descs_d, int n_desc, int lane_slots, int mode, cudaStream_t st);
 
 // ---- device-resident encode: batched startfreq + one-warp-per-stream push (gmm_push.cu) ----
+constexpr int kSfBypassSlots = 15;
 struct SfDesc {
     GmmParamsView p;
     const int32_t* sym;
     uint32_t* packed;         // out: start | freq << 16 per symbol, 0x0000ffff = bypass
     int32_t n;
     int32_t first_block;      // exclusive prefix of ceil(n / 128)
+    uint32_t* flag;           // optional, 32 words, zeroed by the caller: [0] counts the bypass records of the range,
+                              // [1 + 2j], [2 + 2j] = index and symbol value of the j-th (first kSfBypassSlots only)
 };
 cudaError_t launch_gmm_startfreq_batched(const SfDesc* descs_d, int n_desc, int total_blocks, int mode, cudaStream_t st);
 

@@ -31,36 +31,53 @@ namespace {
 
 constexpr uint32_t kFull = 0xffffffffu;
 
+// rANS state + output cursor. Passed and returned BY VALUE everywhere: taking its address (a
+// member function called out of line) would pin it to local memory, and the symbol chain would
+// pay an LDL for the buffer pointer at every renormalisation.
 struct PushState {
     uint32_t xlo, xhi;
-    uint32_t* buf;           // words are written at buf[--pos]
-    uint32_t pos;            // next free slot is pos - 1; counts down from cap
+    uint32_t pos;            // words are written at buf[--pos]; counts down from cap
     uint32_t need;           // words the stream needs in total (keeps counting after an overflow)
-    bool lane0;
-
-    __device__ __forceinline__ void emit(uint32_t w) {
-        ++need;
-        if (pos > 0u) { --pos; if (lane0) buf[pos] = w; }
-    }
-    __device__ __forceinline__ void put_bits4(uint32_t val) {              // Rans64EncPutBits, 4 bits
-        if (xhi >= (1u << 27)) { emit(xlo); xlo = xhi; xhi = 0u; }        // x >= 2^59
-        xhi = (xhi << 4) | (xlo >> 28);
-        xlo = (xlo << 4) | val;
-    }
-    __device__ __forceinline__ void put_marker() {                         // put(65535, 1)
-        if (xhi >= (1u << 15)) { emit(xlo); xlo = xhi; xhi = 0u; }        // x >= 1 << 47
-        xhi = (xhi << 16) | (xlo >> 16);
-        xlo = (xlo << 16) | 65535u;
-    }
-    __device__ __noinline__ void put_bypass(int32_t v) {                // rans_interface.cpp:524-552, reversed
-        const uint32_t raw = (uint32_t)v;
-        int nb = 0;
-        for (uint32_t t = raw; t != 0u; t >>= 4) ++nb;
-        for (int j = nb - 1; j >= 0; --j) put_bits4((raw >> (4 * j)) & 15u);
-        put_bits4((uint32_t)nb);
-        put_marker();
-    }
 };
+
+__device__ __forceinline__ void emit(PushState& S, uint32_t* buf, bool lane0, uint32_t w) {
+    ++S.need;
+    if (S.pos > 0u) { --S.pos; if (lane0) buf[S.pos] = w; }
+}
+__device__ __forceinline__ void put_bits4(PushState& S, uint32_t* buf, bool lane0, uint32_t val) {   // Rans64EncPutBits, 4 bits
+    if (S.xhi >= (1u << 27)) { emit(S, buf, lane0, S.xlo); S.xlo = S.xhi; S.xhi = 0u; }            // x >= 2^59
+    S.xhi = (S.xhi << 4) | (S.xlo >> 28);
+    S.xlo = (S.xlo << 4) | val;
+}
+// rans_interface.cpp:524-552, reversed: value nibbles high to low, the count, then put(65535, 1)
+__device__ __noinline__ PushState put_bypass(PushState S, uint32_t* buf, bool lane0, int32_t v) {
+    const uint32_t raw = (uint32_t)v;
+    int nb = 0;
+    for (uint32_t t = raw; t != 0u; t >>= 4) ++nb;
+    for (int j = nb - 1; j >= 0; --j) put_bits4(S, buf, lane0, (raw >> (4 * j)) & 15u);
+    put_bits4(S, buf, lane0, (uint32_t)nb);
+    if (S.xhi >= (1u << 15)) { emit(S, buf, lane0, S.xlo); S.xlo = S.xhi; S.xhi = 0u; }            // x >= 1 << 47
+    S.xhi = (S.xhi << 16) | (S.xlo >> 16);
+    S.xlo = (S.xlo << 16) | 65535u;
+    return S;
+}
+
+// One symbol of Rans64EncPut (scale_bits 16) on registers, no branch: renormalise when
+// x >= freq << 47, then x = x + start + bias + (x / freq) * (65536 - freq).
+__device__ __forceinline__ void put_symbol(PushState& S, uint32_t* buf, bool lane0, const uint4 e) {
+    const uint32_t freq = e.z >> 16, start = e.z & 0xffffu;
+    const bool spill = S.xhi >= (freq << 15);
+    const bool wr = spill && S.pos > 0u;
+    S.need += spill ? 1u : 0u;
+    S.pos -= wr ? 1u : 0u;
+    if (wr && lane0) buf[S.pos] = S.xlo;
+    const uint32_t lo = spill ? S.xhi : S.xlo, hi = spill ? 0u : S.xhi;
+    const unsigned long long x = ((unsigned long long)hi << 32) | lo;
+    const unsigned long long rcp = ((unsigned long long)e.y << 32) | e.x;
+    const unsigned long long q = __umul64hi(x, rcp) >> (e.w & 0xffffu);
+    const unsigned long long xn = x + start + (e.w >> 16) + q * (unsigned long long)(65536u - freq);
+    S.xlo = (uint32_t)xn; S.xhi = (uint32_t)(xn >> 32);
+}
 
 __global__ void __launch_bounds__(32)
 gmm_push_kernel(const PushDesc* __restrict__ descs, const PushRcp* __restrict__ rcp_tab,
@@ -73,72 +90,58 @@ gmm_push_kernel(const PushDesc* __restrict__ descs, const PushRcp* __restrict__ 
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_begin));
     PushState S;
     S.xlo = 0x80000000u; S.xhi = 0u;                      // RANS64_L = 2^31
-    S.buf = d.buf; S.pos = d.cap_words; S.need = 0u; S.lane0 = lane == 0;
+    S.pos = d.cap_words; S.need = 0u;
+    uint32_t* const buf = d.buf;
+    const bool lane0 = lane == 0;
 
     const int n = d.n;
     const int n_groups = (n + 31) >> 5;
-    // group g covers symbols [n - 32(g+1), n - 32g) (clipped at 0); lane l holds symbol hi - 1 - l
-    auto fetch = [&](int g, int slot) {
+    // group g covers symbols [n - 32(g+1), n - 32g) (clipped at 0); lane l holds symbol n - 1 - 32g - l.
+    // Two loads feed a group: the record, then the reciprocal entry it indexes. Both are issued
+    // well ahead and land in registers while the warp is busy with the chain: records two groups
+    // ahead, reciprocal entries one group ahead; they are parked in shared memory at the END of the
+    // group in between, so the chain never waits for global memory.
+    auto load_pk = [&](int g) -> uint32_t {
         const int i = n - 1 - 32 * g - lane;
-        uint4 e = make_uint4(0u, 0u, 0x00010000u, 0u);     // inert: never read (i < 0 is past the loop bound)
-        if (i >= 0) {
-            const uint32_t pk = __ldg(d.packed + i);
-            const PushRcp r = rcp_tab[pk >> 16];
-            e = make_uint4((uint32_t)r.rcp, (uint32_t)(r.rcp >> 32), pk, (uint32_t)r.shift | ((uint32_t)r.bias << 16));
-        }
-        park[slot][lane] = e;
+        return (g < n_groups && i >= 0) ? __ldg(d.packed + i) : 0x00010000u;       // inert filler, never pushed
     };
-    if (n_groups > 0) fetch(0, 0);
+    auto load_rcp = [&](uint32_t pk) -> uint4 {
+        const PushRcp r = rcp_tab[pk >> 16];
+        return make_uint4((uint32_t)r.rcp, (uint32_t)(r.rcp >> 32), pk, (uint32_t)r.shift | ((uint32_t)r.bias << 16));
+    };
+    uint32_t pk_next = load_pk(1);
+    park[0][lane] = load_rcp(load_pk(0));
     __syncwarp();
 
     for (int g = 0; g < n_groups; ++g) {
-        if (g + 1 < n_groups) fetch(g + 1, (g + 1) & 1);
+        const uint4 e_next = load_rcp(pk_next);              // group g+1's entries: consumed at the end of this group
+        pk_next = load_pk(g + 2);                            // group g+2's records: consumed one group from now
         const int cnt = min(32, n - 32 * g);
         const uint4* slot = park[g & 1];
         // does the group hold a bypass record? (known from the records, not from the state: the
         // common group then runs without a single branch)
         const bool plain = __all_sync(kFull, lane >= cnt || (slot[lane].z >> 16) != 0u);
         if (plain && cnt == 32) {
-            uint32_t xlo = S.xlo, xhi = S.xhi, pos = S.pos, need = S.need;
+            uint4 e = slot[0];
 #pragma unroll
             for (int l = 0; l < 32; ++l) {
-                const uint4 e = slot[l];                    // one 16-byte broadcast
-                const uint32_t freq = e.z >> 16, start = e.z & 0xffffu;
-                // Rans64EncPut, scale_bits 16: renormalise when x >= freq << 47
-                const bool spill = xhi >= (freq << 15);
-                const bool wr = spill && pos > 0u;
-                need += spill ? 1u : 0u;
-                pos -= wr ? 1u : 0u;
-                if (wr && S.lane0) S.buf[pos] = xlo;
-                const uint32_t lo = spill ? xhi : xlo, hi = spill ? 0u : xhi;
-                const unsigned long long x = ((unsigned long long)hi << 32) | lo;
-                const unsigned long long rcp = ((unsigned long long)e.y << 32) | e.x;
-                const unsigned long long q = __umul64hi(x, rcp) >> (e.w & 0xffffu);
-                const unsigned long long xn = x + start + (e.w >> 16) + q * (unsigned long long)(65536u - freq);
-                xlo = (uint32_t)xn; xhi = (uint32_t)(xn >> 32);
+                const uint4 e_cur = e;                       // one 16-byte broadcast, fetched a symbol ahead
+                if (l + 1 < 32) e = slot[l + 1];
+                put_symbol(S, buf, lane0, e_cur);
             }
-            S.xlo = xlo; S.xhi = xhi; S.pos = pos; S.need = need;
         } else {
             for (int l = 0; l < cnt; ++l) {
                 const uint4 e = slot[l];
-                const uint32_t freq = e.z >> 16, start = e.z & 0xffffu;
-                if (freq == 0u) {
-                    S.put_bypass(__ldg(d.sym + (n - 1 - 32 * g - l)));
-                    continue;
-                }
-                if (S.xhi >= (freq << 15)) { S.emit(S.xlo); S.xlo = S.xhi; S.xhi = 0u; }
-                const unsigned long long x = ((unsigned long long)S.xhi << 32) | S.xlo;
-                const unsigned long long rcp = ((unsigned long long)e.y << 32) | e.x;
-                const unsigned long long q = __umul64hi(x, rcp) >> (e.w & 0xffffu);
-                const unsigned long long xn = x + start + (e.w >> 16) + q * (unsigned long long)(65536u - freq);
-                S.xlo = (uint32_t)xn; S.xhi = (uint32_t)(xn >> 32);
+                if ((e.z >> 16) == 0u) S = put_bypass(S, buf, lane0, __ldg(d.sym + (n - 1 - 32 * g - l)));
+                else put_symbol(S, buf, lane0, e);
             }
         }
+        park[(g + 1) & 1][lane] = e_next;
         __syncwarp();
     }
     // Rans64EncFlush: x.hi then x.lo walking backwards -> [x.lo, x.hi] lead the stream
-    S.emit(S.xhi);
-    S.emit(S.xlo);
+    emit(S, buf, lane0, S.xhi);
+    emit(S, buf, lane0, S.xlo);
 
     // hand the words over: claim a slice of `out`, copy the tail of the scratch buffer into it
     const uint32_t used = d.cap_words - S.pos;
@@ -147,7 +150,7 @@ gmm_push_kernel(const PushDesc* __restrict__ descs, const PushRcp* __restrict__ 
     if (lane == 0) off = atomicAdd(out_used, (unsigned long long)used);
     off = __shfl_sync(kFull, off, 0);
     __syncwarp();
-    for (uint32_t k = lane; k < used; k += 32) out[off + k] = d.buf[S.pos + k];
+    for (uint32_t k = lane; k < used; k += 32) out[off + k] = buf[S.pos + k];
     if (lane == 0) {
         d.result[0] = S.need;
         d.result[1] = (uint32_t)off;

@@ -119,19 +119,26 @@ struct RansEncoder64 {
         put(kMaxCdf, 1);
     }
     // symbols [0, cnt) of one chunk, last first. `room` words must be reserved by the caller
-    // (<= 11 words per symbol).
-    inline void push_chunk_reverse(const uint32_t* packed, const int32_t* sym, int64_t cnt) {
+    // (<= 11 words per symbol). sym_at(i) is asked for the value of a bypassed symbol only.
+    template <class SymAt>
+    inline void push_chunk_reverse_with(const uint32_t* packed, int64_t cnt, SymAt sym_at) {
         constexpr int64_t kBlk = 4096;
         for (int64_t hi = cnt; hi > 0; hi -= kBlk) {
             int64_t lo = hi > kBlk ? hi - kBlk : 0;
             out->reserve((size_t)(hi - lo) * 11 + 4);
             for (int64_t i = hi - 1; i >= lo; --i) {
+                // the records sit in page-locked memory the GPU has just written and the walk is
+                // backwards: ask for the lines well ahead
+                if ((i & 15) == 15) __builtin_prefetch(packed + i - 1024, 0, 0);
                 uint32_t pk = packed[i];
                 uint32_t freq = pk >> 16;
                 if (__builtin_expect(freq != 0, 1)) put(pk & 0xffffu, freq);
-                else put_bypass_reverse(sym[i]);
+                else put_bypass_reverse(sym_at(i));
             }
         }
+    }
+    inline void push_chunk_reverse(const uint32_t* packed, const int32_t* sym, int64_t cnt) {
+        push_chunk_reverse_with(packed, cnt, [sym](int64_t i) { return sym[i]; });
     }
     inline void flush() {                                      // Rans64EncFlush
         out->reserve(2);

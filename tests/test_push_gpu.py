@@ -1,6 +1,8 @@
-"""Device-resident encode (batched startfreq kernel + one-warp-per-stream push kernel,
-flashgmm_b200/csrc/gmm_push.cu) against the oracle's restatement of
-BufferedRansEncoder::encode_with_indexes_gmm<4> + flush (rans_interface.cpp:458-585):
+"""Batch encode against the oracle's restatement of
+BufferedRansEncoder::encode_with_indexes_gmm<4> + flush (rans_interface.cpp:458-585), through both
+serial halves the batch call can take -- FLASHGMM_PUSH=device: batched startfreq kernel +
+one-warp-per-stream push kernel (csrc/gmm_push.cu); FLASHGMM_PUSH=host: batched startfreq waves +
+worker-thread pushes (flashgmm_abi.cu::encode_batch_waves) -- and the default split of the two:
 byte-identical streams, bypass payloads included, and the ENOSPC contract of the C ABI."""
 import ctypes as C
 
@@ -14,13 +16,13 @@ from oracle import port
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture()
-def push_ctx(monkeypatch):
-    """A private ctx whose batch encodes always take the device path."""
+@pytest.fixture(params=["device", "host"])
+def push_ctx(monkeypatch, request):
+    """A private ctx whose batch encodes always take the device path / the host waves path."""
     made = []
 
     def make():
-        monkeypatch.setenv("FLASHGMM_PUSH", "device")
+        monkeypatch.setenv("FLASHGMM_PUSH", request.param)
         h = C.c_void_p()
         _lib.check(_lib.lib().flashgmm_ctx_create(0, C.byref(h)))
         made.append(h)
@@ -84,6 +86,9 @@ def test_bypass_payloads_and_int32_extremes(push_ctx, mode):
     sym2 = np.round(mu2[0] + r.standard_normal(n) * sg2[0]).astype(np.int32)
     data.append((sym2, sg2.T, mu2.T, w2.T))
     data.append(synth.gmm_numpy(7, seed=1404))
+    sym, sg, mu, w = synth.gmm_numpy(40000, seed=1405)                                      # a handful of bypasses per wave
+    sym[::5003] = 30000
+    data.append((sym, sg, mu, w))
     got, status, _lens, rc = encode_batch(push_ctx(), data, mode)
     assert rc == 0 and not any(status)
     for g, (sym, sg, mu, w) in zip(got, data):
@@ -101,9 +106,25 @@ def test_output_buffer_too_small_reports_the_needed_size(push_ctx):
     assert rc == 0 and got == want
 
 
-def test_auto_policy_keeps_small_batches_on_the_host_workers():
-    """Default ctx, 6 equal streams, plenty of cores: the cost model leaves the push on the host;
-    either way the bytes are the oracle's."""
+@pytest.mark.parametrize("device", ["cuda", "cpu"])
+def test_default_split_of_an_image_batch(device):
+    """Default ctx, two ELIC-shaped images: the cost model splits the streams between the worker
+    threads and the push kernel; the bytes are the oracle's."""
+    sizes = [12288, 12288, 12288, 12288, 24576, 24576, 49152, 49152, 147456, 147456] * 2
+    data = [synth.gmm_numpy(n, seed=1700 + i) for i, n in enumerate(sizes)]
+    h = C.c_void_p()
+    _lib.check(_lib.lib().flashgmm_ctx_create(0, C.byref(h)))
+    try:
+        got, status, _lens, rc = encode_batch(h, data, 0, device)
+    finally:
+        _lib.lib().flashgmm_ctx_destroy(h)
+    assert rc == 0 and not any(status)
+    for g, (sym, sg, mu, w) in zip(got, data):
+        assert g == port.gmm_encode(sym, sg, mu, w, 0)
+
+
+def test_auto_policy_on_a_small_batch():
+    """Default ctx, 6 equal streams: whatever the cost model decides, the bytes are the oracle's."""
     from flashgmm_b200 import batch
     data = [synth.gmm_numpy(9000 + i, seed=1600 + i) for i in range(6)]
     streams = [(torch.from_numpy(sym).cuda(), kmajor(sg, "cuda"), kmajor(mu, "cuda"), kmajor(w, "cuda"))
