@@ -191,7 +191,8 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
     extern __shared__ __align__(128) uint8_t ring[];
     __shared__ uint64_t bars[kPopStages];
     __shared__ __align__(16) uint32_t bcast[4];
-    __shared__ __align__(16) uint32_t win[kWinWords];
+    __shared__ __align__(16) uint32_t win[2 * kWinWords];    // every block twice, kWinWords apart: a group reads on past the wrap
+    __shared__ uint32_t obuf[32];                            // the group's symbols (lane-local part), posted by the lanes that placed them
     static_assert(!WIN || NI == 1, "the windowed record has one interval per lane");
     constexpr uint32_t kRowBytes = WIN ? 4u * kPopWindowWords : 128u * NI;
     // symbols between two looks at the "somebody could not be placed" count = rows per stage: the
@@ -241,7 +242,9 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
         if (next_blk + 4u < want) next_blk = want - 4u;              // the careful path jumped far ahead
         if (__builtin_expect(next_blk < want, 0)) {
             while (next_blk < want) {
-                win[(next_blk & 3u) * 32u + lane] = S.fetch(next_blk * 32u + lane);
+                const uint32_t wv = S.fetch(next_blk * 32u + lane);
+                win[(next_blk & 3u) * 32u + lane] = wv;
+                win[(next_blk & 3u) * 32u + lane + kWinWords] = wv;
                 ++next_blk;
             }
             __syncwarp();
@@ -250,6 +253,8 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
     feed_window();
 
     const uint32_t bc = smem_addr(bcast);
+    const uint32_t ob = smem_addr(obuf);
+    constexpr uint32_t kUnplaced = 0x80000000u;                       // never a symbol's lane-local part (|.| < 2^11)
     int32_t* out = d.out;
     int sym0 = 0;                                                    // chunk-local index of the stage's first symbol
     int vbase[NI];
@@ -279,62 +284,79 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
             uint32_t rp = stage_base + (uint32_t)r * kRowBytes;
             bool redo = g < kGroup;
             if (!redo) {
-                // ---- 8 symbols, no branch ----
-                uint32_t xlo = S.xlo, xhi = S.xhi, ptr = S.ptr;
-                uint32_t nhit = 0u;                                 // symbols of the group THIS lane placed
+                // ---- kGroup symbols, no branch ----
+                uint32_t xlo = S.xlo, xhi = S.xhi;
                 Ival cur[NI], nxt[NI];
                 load_ivals(rp, cur);
-                uint32_t v0 = 0, nv0 = 0;                           // windowed: symbol value of lane 0's interval
-                if (WIN) v0 = lds_u32(rp - kLaneOff0 - kLaneStride * lane);
-                uint32_t wnext = lds_u32(win_base + ((ptr << 2) & (4u * kWinWords - 4u)));
+                // next stream word: the window holds every block twice, so the cursor just walks on
+                const uint32_t w0 = win_base + ((S.ptr << 2) & (4u * kWinWords - 4u));
+                uint32_t waddr = w0;
+                uint32_t wnext = lds_u32(waddr);
+                obuf[lane] = kUnplaced;
+                __syncwarp();
 #pragma unroll
                 for (int i = 0; i < kGroup; ++i) {
                     rp += kRowBytes;
-                    if (i + 1 < kGroup) {                            // next row: independent of the chain
-                        load_ivals(rp, nxt);
-                        if (WIN) nv0 = lds_u32(rp - kLaneOff0 - kLaneStride * lane);
-                    }
+                    if (i + 1 < kGroup) load_ivals(rp, nxt);         // next row: independent of the chain
                     const uint32_t cum = xlo & 0xffffu;
                     const uint32_t xs_lo = __funnelshift_r(xlo, xhi, 16), xs_hi = xhi >> 16;
                     uint32_t clo = 0, chi = 0;
-                    int v = 0;
+                    uint64_t c64 = 0;                                // NI == 1: the candidate as one register pair
+                    int v = lane;                                    // windowed: the record's word 0 is added when the group is written out
                     bool hit = false;
 #pragma unroll
                     for (int k = 0; k < NI; ++k) {
                         const uint32_t lo = cur[k].lo, wd = cur[k].wd;
                         const uint32_t dk = cum - lo;
-                        const uint64_t ck = (uint64_t)wd * xs_lo + dk + ((uint64_t)(wd * xs_hi) << 32);
                         const bool hk = dk < wd;         // never true for cum == 65535: start + width <= 65535
-                        if (hk) { clo = (uint32_t)ck; chi = (uint32_t)(ck >> 32); v = vbase[k]; }
+                        if constexpr (NI == 1) {
+                            // the candidate is formed BESIDE the compare (the empty volatile asm pins it
+                            // there: the compiler would otherwise sink both multiplies under the hit
+                            // predicate, behind the compare)
+                            c64 = (uint64_t)wd * xs_lo + dk + ((uint64_t)(wd * xs_hi) << 32);
+                            asm volatile("" : "+l"(c64));
+                            if (!WIN) v = vbase[0];
+                        } else {
+                            const uint64_t ck = (uint64_t)wd * xs_lo + dk + ((uint64_t)(wd * xs_hi) << 32);
+                            if (hk) { clo = (uint32_t)ck; chi = (uint32_t)(ck >> 32); v = vbase[k]; }
+                        }
                         hit |= hk;
                     }
-                    if (WIN) v += (int)v0;
                     // the winner posts its state, everyone reads it back (the LSU keeps one warp's shared
                     // accesses in program order). If no lane can place cum the slot keeps its old content
-                    // and the group runs on with garbage: the hit count comes up short and the group is
-                    // redone below. (Measured against REDUX.OR x2, a 128-bit slot that also carries the
-                    // symbol, and posting the row word with the multiply after the read-back: this is the
-                    // fastest of the four by 5-12 %, profiles/r01_s12_pop_variants.txt.)
+                    // and the group runs on with garbage: the symbol's obuf slot stays kUnplaced and the
+                    // group is redone below. (Measured against REDUX.OR x2, a 128-bit slot that also
+                    // carries the symbol, and posting the row word with the multiply after the read-back:
+                    // this is the fastest of the four by 5-12 %, profiles/r01_s12_pop_variants.txt.)
                     uint32_t rlo, rhi;
-                    if (hit) asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(bc), "r"(clo), "r"(chi) : "memory");
+                    if constexpr (NI == 1) {
+                        if (hit) asm volatile("st.shared.u64 [%0], %1;" ::"r"(bc), "l"(c64) : "memory");
+                    } else {
+                        if (hit) asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(bc), "r"(clo), "r"(chi) : "memory");
+                    }
                     asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(rlo), "=r"(rhi) : "r"(bc) : "memory");
-                    if (hit) out[r + i] = v;
-                    nhit += hit ? 1u : 0u;
+                    if (hit) asm volatile("st.shared.u32 [%0], %1;" ::"r"(ob + 4u * (uint32_t)i), "r"(v) : "memory");
                     const bool need = rhi == 0u && rlo < 0x80000000u;                // rans64.h:136-141
                     xhi = need ? rlo : rhi;
                     xlo = need ? wnext : rlo;
-                    ptr += need ? 1u : 0u;
-                    if (need) wnext = lds_u32(win_base + ((ptr << 2) & (4u * kWinWords - 4u)));
+                    if (need) { waddr += 4u; wnext = lds_u32(waddr); }
 #pragma unroll
                     for (int k = 0; k < NI; ++k) cur[k] = nxt[k];
-                    v0 = nv0;
                 }
-                if (__builtin_expect(__reduce_add_sync(kFull, nhit) == (uint32_t)kGroup, 1)) {   // every symbol placed
-                    S.xlo = xlo; S.xhi = xhi; S.ptr = ptr;
+                __syncwarp();
+                const uint32_t mine = obuf[lane & (kGroup - 1)];     // lane i answers for symbol i of the group
+                if (__builtin_expect(__all_sync(kFull, mine != kUnplaced), 1)) {     // every symbol placed
+                    S.xlo = xlo; S.xhi = xhi; S.ptr += (waddr - w0) >> 2;
+                    if (lane < kGroup) {
+                        const uint32_t row0 = stage_base - kLaneOff0 - kLaneStride * lane + (uint32_t)(r + lane) * kRowBytes;
+                        const int v0 = WIN ? (int)lds_u32(row0) : 0;
+                        out[r + lane] = (int)mine + v0;              // one coalesced store per group
+                    }
                 } else {
                     redo = true;
                     rp = stage_base + (uint32_t)r * kRowBytes;
                 }
+                __syncwarp();                                        // obuf is rewritten by the next group
             }
             if (redo) {
                 // ---- symbol by symbol from the group's first state: literal path where needed ----
