@@ -339,7 +339,8 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
                     const bool need = rhi == 0u && rlo < 0x80000000u;                // rans64.h:136-141
                     xhi = need ? rlo : rhi;
                     xlo = need ? wnext : rlo;
-                    if (need) { waddr += 4u; wnext = lds_u32(waddr); }
+                    waddr += need ? 4u : 0u;                         // unconditional reload: two instructions instead of
+                    wnext = lds_u32(waddr);                          // five predicated ones, and it is needed a symbol later at the earliest
 #pragma unroll
                     for (int k = 0; k < NI; ++k) cur[k] = nxt[k];
                 }
