@@ -38,10 +38,10 @@ ELIC_GROUPS = (16, 16, 32, 64, 192)          # elic_gmm.py:92-93
 LATENT_HW = (32, 48)                         # 512x768 / 16
 N_SETS = 2                                   # rotating batches of images (each batch > 126 MB L2 for B >= 5)
 # (dram__bytes_read.sum + dram__bytes_write.sum) / symbols of the captured launch, from the committed
-# ncu --set full captures (profiles/r01_s20_ncu_full_*.csv: batched startfreq 4.72 M symbols, rows
+# ncu --set full captures (profiles/r01_s22_ncu_full_*.csv: batched startfreq 786 432 symbols, rows
 # 786 432, pop 589 824, push 4.72 M); multiplied by the symbols per launch of this run to give
 # `traffic` per launch.
-NCU_DRAM_BYTES_PER_SYMBOL = {"gmm_startfreq": 55.3, "gmm_cdf_rows": 245.5, "gmm_pop_rows": 373.6, "gmm_push": 4.2}
+NCU_DRAM_BYTES_PER_SYMBOL = {"gmm_startfreq": 52.1, "gmm_cdf_rows": 246.0, "gmm_pop_rows": 373.5, "gmm_push": 4.2}
 ALGO_BYTES_PER_SYMBOL = {"gmm_startfreq": 56.0, "gmm_cdf_rows": 48.0 + 272.0, "gmm_pop_rows": 272.0 + 4.0, "gmm_push": 4.0 + 8.0 * 0.14}
 
 
@@ -288,7 +288,7 @@ def run_b200(args):
         "gmm_cdf_rows": "FP32-issue-bound by construction (2R+2 = 46 CDF points x 4 components per symbol, ~10 k "
                         "thread-instructions per symbol); DESIGN.md section 5",
         "gmm_pop_rows": "latency-bound by construction: the rANS state recurrence is serial per stream, one warp per "
-                        "stream, ~115 cycles per symbol; HBM fraction is not the figure of merit, ns/symbol/stream is",
+                        "stream, ~100 cycles per symbol; HBM fraction is not the figure of merit, ns/symbol/stream is",
         "gmm_push": "latency-bound by construction: the rANS state recurrence is serial per stream, one warp per "
                     "stream, ~95 cycles per symbol; runs beside the host worker threads on the shorter streams",
     }

@@ -1116,6 +1116,18 @@ int encode_batch_device_finish(flashgmm_ctx* ctx, flashgmm_stream* streams) {
         t_first = std::min(t_first, (unsigned long long)hr[8 * a + 4] | ((unsigned long long)hr[8 * a + 5] << 32));
         t_last = std::max(t_last, (unsigned long long)hr[8 * a + 6] | ((unsigned long long)hr[8 * a + 7] << 32));
     }
+    static const bool dtrace = env_long("FLASHGMM_TRACE", 0) != 0;
+    if (dtrace) {
+        unsigned long long latest_start = 0, longest = 0;
+        for (int a = 0; a < na; ++a) {
+            const unsigned long long b = (unsigned long long)hr[8 * a + 4] | ((unsigned long long)hr[8 * a + 5] << 32);
+            const unsigned long long e = (unsigned long long)hr[8 * a + 6] | ((unsigned long long)hr[8 * a + 7] << 32);
+            latest_start = std::max(latest_start, b - t_first);
+            longest = std::max(longest, e - b);
+        }
+        fprintf(stderr, "[flashgmm trace] push kernel ran %.3f ms (its own %%globaltimer stamps): last warp started at %.3f ms, longest warp %.3f ms\n",
+                (double)(t_last - t_first) * 1e-6, (double)latest_start * 1e-6, (double)longest * 1e-6);
+    }
     if (prof) {
         float a = 0;
         cudaEventElapsedTime(&a, E.t[0], E.t[1]);
@@ -1610,15 +1622,22 @@ int flashgmm_gmm_encode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     // the calling thread queues the device part (asynchronous), takes its share of the host part,
     // then collects the device part
     std::lock_guard<std::mutex> dg(ctx->de_mu);
+    static const bool btrace = env_long("FLASHGMM_TRACE", 0) != 0;
+    const auto bt0 = std::chrono::steady_clock::now();
+    auto bms = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - bt0).count(); };
     int dev_rc = encode_batch_device_begin(ctx, dev_part.data(), (int)dev_part.size(), mode, mem);
+    const double bt_begin = bms();
     const bool dev_queued = dev_rc == FLASHGMM_OK;
     // host inputs: the device part's parameters cross PCIe first (its push then runs while the host
     // part's cross), instead of both halving the link
     cudaEvent_t gate = (dev_queued && mem == FLASHGMM_MEM_HOST && !ctx->de->act.empty()) ? ctx->de->ev_sf : nullptr;
     int host_rc = host_part.empty() ? FLASHGMM_OK : host_encode(host_part.data(), (int)host_part.size(), gate);
+    const double bt_host = bms();
     if (dev_queued) {
         const std::string host_err = host_rc ? g_err : std::string();
         dev_rc = encode_batch_device_finish(ctx, dev_part.data());
+        if (btrace) fprintf(stderr, "[flashgmm trace] encode batch: device part queued %.2f ms, host part done %.2f ms, device part collected %.2f ms\n",
+                            bt_begin, bt_host, bms());
         if (host_rc) g_err = host_err;
     } else if (dev_rc < 0) {                                 // pageable host tensors: the workers take them too
         dev_rc = host_encode(dev_part.data(), (int)dev_part.size(), nullptr);
