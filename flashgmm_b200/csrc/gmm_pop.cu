@@ -20,13 +20,14 @@
 //   LOP (cum) -> IADD/ISETP (does cum fall in this lane's interval?) ->
 //   STS (the winner posts its new state) -> LDS (every lane reads it) -> refill select
 // and keeps everything else off it:
-//   * the rows kernel hands each lane its intervals ready-made (start and width as two
-//     uint16 planes, one LDS.U16 each, no unpacking) and rows reach shared memory through
+//   * the rows kernel hands each lane its interval ready-made (start and width as two 32-bit
+//     words, one LDS.64, no unpacking) and rows reach shared memory through
 //     a ring of 1-D TMA bulk copies (cp.async.bulk + mbarrier) issued by lane 0;
 //   * every lane forms its candidate state beside the compare;
-//   * symbols run in groups of 8 with NO branch inside a group: after a symbol no lane can
-//     place the group runs on with garbage; the lanes' hit counts are summed once per
-//     group, and if one is missing the group is rolled back and redone symbol by symbol;
+//   * symbols run in groups of 32 with NO branch inside a group: after a symbol no lane can
+//     place the group runs on with garbage; the lane that places a symbol posts it into a
+//     shared-memory buffer, and a slot left untouched rolls the group back to be redone symbol
+//     by symbol; a placed group is written out with one coalesced store;
 //   * stream words come from a 128-word shared-memory window refilled between groups.
 //
 // Lane l owns the intervals j = l + 32k (k < NI): hit iff T[j] <= cum < T[j+1]. On a

@@ -220,3 +220,19 @@ def test_pinned_host_tensors_are_read_in_place(n_streams):
     outs = batch.decode_batch([(b, st[1], st[2], st[3], synth.search_radius(d[0])) for b, st, d in zip(want, enc_in, data)], 0)
     for o, d in zip(outs, data):
         assert o.device.type == "cpu" and np.array_equal(o.numpy(), d[0])
+
+
+def test_more_length_classes_than_pop_groups(pop_ctx):
+    """Stream lengths over four orders of magnitude: more length classes than the decoder has pop
+    streams (the shortest classes share the last group), ragged lengths inside a group."""
+    sizes = [3, 9, 40, 130, 500, 1100, 2300, 5000, 5100, 9000, 20000, 41000, 90000, 7, 2400]
+    items, want = [], []
+    for i, n in enumerate(sizes):
+        sym, sg, mu, w = synth.gmm_numpy(n, seed=2000 + i)
+        items.append((port.gmm_encode(sym, sg, mu, w, 0), sg, mu, w, synth.search_radius(sym)))
+        want.append(sym)
+    for device in ("cuda", "cpu"):
+        got, status, rc = decode_batch(pop_ctx(), items, 0, device)
+        assert rc == 0 and not any(status)
+        for g, wd in zip(got, want):
+            assert np.array_equal(g, wd)

@@ -131,3 +131,41 @@ def test_auto_policy_on_a_small_batch():
                for sym, sg, mu, w in data]
     got = batch.encode_batch(streams, 0)
     assert got == [port.gmm_encode(*d, 0) for d in data]
+
+
+def test_pageable_host_tensors_fall_back_to_the_per_stream_path(push_ctx):
+    """Pageable (not page-locked) host tensors cannot be read in place: both batch halves hand the
+    streams to the staging path; same bytes."""
+    data = [synth.gmm_numpy(6000 + 37 * i, seed=1800 + i) for i in range(5)]
+    n = len(data)
+    arr = (_lib.Stream * n)()
+    keep, outs = [], []
+    for i, (sym, sg, mu, w) in enumerate(data):
+        s = np.ascontiguousarray(sym)
+        a, m, ww = (np.ascontiguousarray(x.T) for x in (sg, mu, w))          # K-major planes, pageable
+        out = np.zeros(44 * sym.size + 64, np.uint8)
+        keep += [s, a, m, ww]
+        outs.append(out)
+        arr[i].symbols, arr[i].scales, arr[i].means, arr[i].weights = (x.ctypes.data for x in (s, a, m, ww))
+        arr[i].n, arr[i].stride_n, arr[i].stride_k = sym.size, 1, sym.size
+        arr[i].bytes, arr[i].bytes_cap = out.ctypes.data, out.size
+    rc = _lib.lib().flashgmm_gmm_encode_batch(push_ctx(), arr, n, 0, _lib.MEM_HOST)
+    assert rc == 0
+    for i, d in enumerate(data):
+        assert outs[i][: arr[i].bytes_len].tobytes() == port.gmm_encode(*d, 0)
+
+
+def test_one_worker_thread(monkeypatch):
+    """FLASHGMM_WORKERS=1: the wave tasks of all streams run on a single worker, in order."""
+    monkeypatch.setenv("FLASHGMM_WORKERS", "1")
+    monkeypatch.setenv("FLASHGMM_PUSH", "host")
+    h = C.c_void_p()
+    _lib.check(_lib.lib().flashgmm_ctx_create(0, C.byref(h)))
+    try:
+        data = [synth.gmm_numpy(n, seed=1900 + i) for i, n in enumerate([30000, 1, 9000, 0, 17000, 40000])]
+        got, status, _lens, rc = encode_batch(h, data, 0)
+    finally:
+        _lib.lib().flashgmm_ctx_destroy(h)
+    assert rc == 0 and not any(status)
+    for g, d in zip(got, data):
+        assert g == port.gmm_encode(*d, 0)
