@@ -127,6 +127,31 @@ def to_pinned(torch, streams):
     return out
 
 
+def bind_to_gpu_cpus(local_rank):
+    """Several ranks on one box: run this rank (its worker threads, its page-locked buffers, which
+    are first touched here) on the CPUs NVML reports as local to its GPU, so that host<->device
+    traffic does not cross the socket interconnect. Returns the number of CPUs bound to, or None."""
+    if os.environ.get("FLASHGMM_BENCH_NO_BIND"):
+        return None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        idx = local_rank
+        if vis and all(v.strip().isdigit() for v in vis.split(",")):
+            idx = int(vis.split(",")[local_rank])
+        h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, ((os.cpu_count() or 64) + 63) // 64)
+        cpus = {64 * i + b for i, wd in enumerate(words) for b in range(64) if (wd >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception:
+        return None
+
+
 def run_b200(args):
     import ctypes as C
 
@@ -146,6 +171,7 @@ def run_b200(args):
     if world > 1 and "FLASHGMM_WORKERS" not in os.environ:
         lws = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
         os.environ["FLASHGMM_WORKERS"] = str(max(1, min(16, (os.cpu_count() or 1) // max(1, lws) - 1)))
+    numa_cpus = bind_to_gpu_cpus(local) if world > 1 else None
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -324,7 +350,7 @@ def run_b200(args):
                              "come down wave by wave), the rest on the device (push kernel, one warp per stream), "
                              "split by a cost model (FLASHGMM_PUSH)",
                    "host_workers": int(os.environ.get("FLASHGMM_WORKERS", "0")) or min(16, max(1, (os.cpu_count() or 2) - 1)),
-                   "host_cores": os.cpu_count()},
+                   "host_cores": os.cpu_count(), "cpus_bound_to_gpu_locality": numa_cpus},
         "encode_ms_per_image": round(1e3 * enc_t / B, 4), "decode_ms_per_image": round(1e3 * dec_t / B, 4),
         "encode_msym_s": round(nsym * B / enc_t / 1e6, 2), "decode_msym_s": round(nsym * B / dec_t / 1e6, 2),
         "latency_single_image_ms": {"encode": round(1e3 * statistics.median(lat_e), 4),
