@@ -62,6 +62,11 @@ _SIGS = {
                                               C.c_float, _vp, _vp, _vp]),
     "flashgmm_gmm_likelihood_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, C.c_int, C.c_float,
                                               C.c_float, _vp, _vp, _vp, _vp, _vp]),
+    "flashgmm_gmm_prologue_scan": (C.c_int, [_vp, _vp, _i64, _i64, _vp, _vp, _vp, C.POINTER(C.c_float),
+                                             C.POINTER(C.c_float), _vp]),
+    "flashgmm_gmm_prologue_gather": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, C.c_int, _i64, _vp, _vp, _vp,
+                                               _vp, _vp]),
+    "flashgmm_gmm_epilogue_scatter": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _vp, _vp]),
     "flashgmm_rans_push_packed": (C.c_int, [_vp, _vp, _i64, _vp, _sz, C.POINTER(_sz)]),
     "flashgmm_rans_pop_table": (C.c_int, [_vp, _sz, _vp, _i64, _i64, _i32, _vp]),
     "flashgmm_rans_encode_table": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _sz, C.POINTER(_sz)]),

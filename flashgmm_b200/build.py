@@ -29,6 +29,7 @@ UNITS = [
     ("gmm_ileave.cu", ["-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false"]),
     ("gmm_pop.cu", ["-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false", "-Xptxas", "-v"]),
     ("gmm_push.cu", ["-Xptxas", "-v"]),
+    ("gmm_prologue.cu", []),
     ("gmm_likelihood.cu", ["-Xptxas", "-v"]),
     ("flashgmm_abi.cu", ["-Xcompiler", "-march=x86-64-v3"]),
 ]

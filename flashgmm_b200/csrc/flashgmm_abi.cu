@@ -340,6 +340,8 @@ struct flashgmm_ctx {
     // device-resident encode (startfreq kernel -> push kernel): chosen per call by a cost model
     std::unique_ptr<DevEncode> de;
     std::unique_ptr<HostWaves> hw;
+    DevBuf pr_dev;                    // compress prologue: extrema codes + bitmap
+    PinBuf pr_host;
     std::mutex de_mu;                 // the device encode path owns its buffers and stream: it runs beside the workers
     int push_policy = 0;              // 0 auto, 1 always host workers, 2 always device
     double push_host_ns = 4.5, push_dev_ns = 46.0;   // per symbol: one host worker / one device warp (measured, B200 box)
@@ -1522,6 +1524,7 @@ void flashgmm_ctx_destroy(flashgmm_ctx* ctx) {
     if (ctx->dd) ctx->dd->destroy();
     if (ctx->de) ctx->de->destroy();
     if (ctx->hw) ctx->hw->destroy();
+    ctx->pr_dev.release(); ctx->pr_host.release();
     ctx->il_scratch.release(); ctx->il_segw.release(); ctx->il_out.release(); ctx->il_err.release();
     ctx->il_host.release();
     delete ctx;
@@ -1654,6 +1657,62 @@ int flashgmm_gmm_decode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     if (n_streams < 0 || (n_streams > 0 && !streams)) return fail(FLASHGMM_EINVAL, "bad stream array");
     if (want_device_pop(ctx, streams, n_streams)) return decode_batch_device(ctx, streams, n_streams, mode, mem);
     return run_batch(ctx, streams, n_streams, mode, mem, decode_stream);
+}
+
+// ---- compress / decompress glue ----
+int flashgmm_gmm_prologue_scan(flashgmm_ctx* ctx, const float* y_d, int64_t C, int64_t HW, float* yq_out_d,
+                               int64_t* bitmap_out_d, int32_t* bitmap_out_h, float* y_max_h, float* y_min_h,
+                               void* stream) {
+    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
+    if (C < 0 || HW < 0 || C > (1 << 20)) return fail(FLASHGMM_EINVAL, "bad shape C=%lld HW=%lld", (long long)C, (long long)HW);
+    if (C > 0 && HW > 0 && (!y_d || !yq_out_d)) return fail(FLASHGMM_EINVAL, "null tensor");
+    if (!bitmap_out_h || !y_max_h || !y_min_h) return fail(FLASHGMM_EINVAL, "null host output");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CU_TRY(cudaSetDevice(ctx->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CU_TRY(ctx->pr_dev.need((size_t)(C + 2) * 4));
+    CU_TRY(ctx->pr_host.need((size_t)(C + 2) * 4));
+    uint32_t* d = static_cast<uint32_t*>(ctx->pr_dev.p);          // [0..1] extrema codes, [2..] bitmap32
+    CU_TRY(launch_gmm_prologue_scan(y_d, (int)C, HW, yq_out_d, reinterpret_cast<long long*>(bitmap_out_d),
+                                    reinterpret_cast<int32_t*>(d + 2), d, st));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU_TRY(cudaMemcpyAsync(ctx->pr_host.p, d, (size_t)(C + 2) * 4, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    const uint32_t* h = static_cast<const uint32_t*>(ctx->pr_host.p);
+    const bool empty = C == 0 || HW == 0;
+    *y_max_h = empty ? 0.0f : gmm_extremum_from_bits(h[0]);
+    *y_min_h = empty ? 0.0f : gmm_extremum_from_bits(h[1]);
+    memcpy(bitmap_out_h, h + 2, (size_t)C * 4);
+    return FLASHGMM_OK;
+}
+
+int flashgmm_gmm_prologue_gather(flashgmm_ctx* ctx, const float* yq_d, const float* scales_d, const float* means_d,
+                                 const float* weights_d, const int64_t* bitmap_d, int64_t C, int64_t HW, int K,
+                                 int64_t n_sym, int32_t* symbols_out_d, float* scales_out_d, float* means_out_d,
+                                 float* weights_out_d, void* stream) {
+    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
+    if (C < 0 || HW < 0 || n_sym < 0 || K < 1 || K > 8 || C > (1 << 20) || (HW > 0 && n_sym % HW != 0))
+        return fail(FLASHGMM_EINVAL, "bad shape C=%lld HW=%lld K=%d n_sym=%lld", (long long)C, (long long)HW, K, (long long)n_sym);
+    if (n_sym > 0 && (!scales_d || !means_d || !weights_d || !bitmap_d || !scales_out_d || !means_out_d || !weights_out_d))
+        return fail(FLASHGMM_EINVAL, "null tensor");
+    CU_TRY(cudaSetDevice(ctx->device));
+    CU_TRY(launch_gmm_prologue_gather(yq_d, scales_d, means_d, weights_d, reinterpret_cast<const long long*>(bitmap_d),
+                                      (int)C, HW, K, n_sym, symbols_out_d, scales_out_d, means_out_d, weights_out_d,
+                                      static_cast<cudaStream_t>(stream)));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return FLASHGMM_OK;
+}
+
+int flashgmm_gmm_epilogue_scatter(flashgmm_ctx* ctx, const int32_t* symbols_d, const int64_t* bitmap_d, int64_t C,
+                                  int64_t HW, float* y_hat_out_d, void* stream) {
+    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
+    if (C < 0 || HW < 0 || C > (1 << 20)) return fail(FLASHGMM_EINVAL, "bad shape C=%lld HW=%lld", (long long)C, (long long)HW);
+    if (C > 0 && HW > 0 && (!bitmap_d || !y_hat_out_d)) return fail(FLASHGMM_EINVAL, "null tensor");
+    CU_TRY(cudaSetDevice(ctx->device));
+    CU_TRY(launch_gmm_epilogue_scatter(symbols_d, reinterpret_cast<const long long*>(bitmap_d), (int)C, HW, y_hat_out_d,
+                                       static_cast<cudaStream_t>(stream)));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return FLASHGMM_OK;
 }
 
 // ---- interleaved multi-lane rANS ----

@@ -118,4 +118,15 @@ cudaError_t launch_gmm_likelihood_bwd(const float* y, const float* sc, const flo
                                       float lik_bound, float* gy, float* gsc, float* gmu, float* gw,
                                       cudaStream_t st);
 
+// ---- compress / decompress glue (gmm_prologue.cu) ----
+cudaError_t launch_gmm_prologue_scan(const float* y, int C, int64_t HW, float* yq, long long* bitmap64,
+                                     int32_t* bitmap32, uint32_t* extrema, cudaStream_t st);
+cudaError_t launch_gmm_prologue_gather(const float* yq, const float* scales, const float* means, const float* weights,
+                                       const long long* bitmap, int C, int64_t HW, int K, int64_t n_sym,
+                                       int32_t* sym_out, float* scales_out, float* means_out, float* weights_out,
+                                       cudaStream_t st);
+cudaError_t launch_gmm_epilogue_scatter(const int32_t* symbols, const long long* bitmap, int C, int64_t HW,
+                                        float* y_hat, cudaStream_t st);
+float gmm_extremum_from_bits(uint32_t code);      // inverse of the order-preserving code the scan kernel reduces with
+
 }  // namespace flashgmm

@@ -1,0 +1,166 @@
+// gmm_prologue.cu -- the glue of GaussianMixtureConditional.compress / decompress ON the GPU
+// (sm_100a): what the reference does with a dozen tensor ops, three host syncs and four
+// device->host copies per call (/root/reference/compressai/entropy_models/entropy_models.py):
+//   compress  :833-851  abs_max from max / min of y, y_quantized = round(y), per-channel
+//                       zero bitmap (sum |y_quantized| over H, W == 0), kept channels compacted
+//                       into the symbol vector, parameters reshaped to (Nsym, K) K-major views
+//                       with the scale clamp (reshape_entropy_parameters, :810-828)
+//   decompress:902-909  decoded symbols scattered back into zeros (1, C, H, W)
+// Three kernels, all plain streaming (HBM-bound, coalesced, no reuse -> no shared-memory
+// staging, no tensor cores):
+//   scan    one CTA per channel: round, "any nonzero", running max / min of the unrounded y
+//   gather  one CTA per (plane, channel): kept channels' rows copied to their compacted place
+//           (exclusive prefix of the bitmap recomputed per CTA: C is a few hundred)
+//   scatter one CTA per channel: symbols back to float rows, zero rows for dropped channels
+// Layouts are the reference's: y (1, C, H, W) contiguous; parameters (1, K*C, H, W) contiguous,
+// component k of channel c at channel k*C + c; outputs [K][Nkept*HW] planes, i.e. the (Nsym, K)
+// views with strides (1, Nsym) the coder reads.
+#include "gmm_kernels.h"
+
+namespace flashgmm {
+
+namespace {
+
+constexpr int kPrThreads = 256;
+
+// order-preserving map float -> uint32 (so that atomicMax / atomicMin work on floats of either sign)
+__device__ __forceinline__ uint32_t ordered_bits(float f) {
+    const uint32_t b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+__global__ void __launch_bounds__(kPrThreads)
+gmm_prologue_scan_kernel(const float* __restrict__ y, int64_t HW, float* __restrict__ yq,
+                         long long* __restrict__ bitmap64, int32_t* __restrict__ bitmap32,
+                         uint32_t* __restrict__ extrema) {
+    __shared__ float s_mx[kPrThreads / 32], s_mn[kPrThreads / 32];
+    __shared__ int s_any[kPrThreads / 32];
+    const int64_t base = (int64_t)blockIdx.x * HW;
+    float mx = -INFINITY, mn = INFINITY;
+    int any = 0;
+    for (int64_t i = threadIdx.x; i < HW; i += kPrThreads) {
+        const float v = __ldg(y + base + i);
+        const float r = rintf(v);                          // torch.round: half to even
+        yq[base + i] = r;
+        any |= (r != 0.0f) ? 1 : 0;                        // sum |r| == 0  <=>  every r == +-0 (NaN counts as nonzero, as there)
+        mx = fmaxf(mx, v);
+        mn = fminf(mn, v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        any |= __shfl_xor_sync(0xffffffffu, any, o);
+    }
+    const int wid = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) { s_mx[wid] = mx; s_mn[wid] = mn; s_any[wid] = any; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < kPrThreads / 32; ++w) { mx = fmaxf(mx, s_mx[w]); mn = fminf(mn, s_mn[w]); any |= s_any[w]; }
+        if (bitmap64) bitmap64[blockIdx.x] = any;
+        bitmap32[blockIdx.x] = any;
+        if (HW > 0) {
+            atomicMax(extrema + 0, ordered_bits(mx));
+            atomicMin(extrema + 1, ordered_bits(mn));
+        }
+    }
+}
+
+// exclusive prefix of the 0/1 bitmap at channel c, by the whole CTA
+__device__ __forceinline__ int kept_before(const long long* __restrict__ bitmap, int c, int* s_part) {
+    int cnt = 0;
+    for (int i = threadIdx.x; i < c; i += kPrThreads) cnt += bitmap[i] != 0 ? 1 : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = cnt;
+    __syncthreads();
+    int tot = 0;
+    for (int w = 0; w < kPrThreads / 32; ++w) tot += s_part[w];
+    return tot;
+}
+
+// grid (C, 3K + 1): plane p < K scales (clamped), < 2K means, < 3K weights, == 3K symbols
+__global__ void __launch_bounds__(kPrThreads)
+gmm_prologue_gather_kernel(const float* __restrict__ yq, const float* __restrict__ scales,
+                           const float* __restrict__ means, const float* __restrict__ weights,
+                           const long long* __restrict__ bitmap, int C, int64_t HW, int K, int64_t n_sym,
+                           int32_t* __restrict__ sym_out, float* __restrict__ scales_out,
+                           float* __restrict__ means_out, float* __restrict__ weights_out) {
+    __shared__ int s_part[kPrThreads / 32];
+    const int c = blockIdx.x, p = blockIdx.y;
+    if (bitmap[c] == 0) return;
+    if (p == 3 * K && (yq == nullptr || sym_out == nullptr)) return;
+    const int64_t j = kept_before(bitmap, c, s_part);
+    if (p == 3 * K) {
+        const float* src = yq + (int64_t)c * HW;
+        int32_t* dst = sym_out + j * HW;
+        for (int64_t i = threadIdx.x; i < HW; i += kPrThreads) dst[i] = (int32_t)__ldg(src + i);   // .int(): truncation
+        return;
+    }
+    const int t = p / K, k = p - t * K;
+    const float* src = (t == 0 ? scales : t == 1 ? means : weights) + ((int64_t)k * C + c) * HW;
+    float* dst = (t == 0 ? scales_out : t == 1 ? means_out : weights_out) + (int64_t)k * n_sym + j * HW;
+    if (t == 0) {
+        for (int64_t i = threadIdx.x; i < HW; i += kPrThreads) {
+            const float v = __ldg(src + i);
+            dst[i] = v < 0.11f ? 0.11f : (v > 256.0f ? 256.0f : v);      // torch.clamp(0.11, 256): NaN stays NaN
+        }
+    } else {
+        for (int64_t i = threadIdx.x; i < HW; i += kPrThreads) dst[i] = __ldg(src + i);
+    }
+}
+
+__global__ void __launch_bounds__(kPrThreads)
+gmm_epilogue_scatter_kernel(const int32_t* __restrict__ symbols, const long long* __restrict__ bitmap,
+                            int64_t HW, float* __restrict__ y_hat) {
+    __shared__ int s_part[kPrThreads / 32];
+    const int c = blockIdx.x;
+    float* dst = y_hat + (int64_t)c * HW;
+    if (bitmap[c] == 0) {
+        for (int64_t i = threadIdx.x; i < HW; i += kPrThreads) dst[i] = 0.0f;
+        return;
+    }
+    const int64_t j = kept_before(bitmap, c, s_part);
+    const int32_t* src = symbols + j * HW;
+    for (int64_t i = threadIdx.x; i < HW; i += kPrThreads) dst[i] = (float)__ldg(src + i);
+}
+
+}  // namespace
+
+cudaError_t launch_gmm_prologue_scan(const float* y, int C, int64_t HW, float* yq, long long* bitmap64,
+                                     int32_t* bitmap32, uint32_t* extrema, cudaStream_t st) {
+    // extrema[0] collects the max (starts at the smallest code), extrema[1] the min (starts at the largest)
+    cudaError_t e = cudaMemsetAsync(extrema, 0x00, 4, st);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(extrema + 1, 0xff, 4, st);
+    if (e != cudaSuccess) return e;
+    if (C <= 0) return cudaSuccess;
+    gmm_prologue_scan_kernel<<<C, kPrThreads, 0, st>>>(y, HW, yq, bitmap64, bitmap32, extrema);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_gmm_prologue_gather(const float* yq, const float* scales, const float* means, const float* weights,
+                                       const long long* bitmap, int C, int64_t HW, int K, int64_t n_sym,
+                                       int32_t* sym_out, float* scales_out, float* means_out, float* weights_out,
+                                       cudaStream_t st) {
+    if (C <= 0 || HW <= 0 || n_sym <= 0) return cudaSuccess;
+    gmm_prologue_gather_kernel<<<dim3((unsigned)C, (unsigned)(3 * K + 1)), kPrThreads, 0, st>>>(
+        yq, scales, means, weights, bitmap, C, HW, K, n_sym, sym_out, scales_out, means_out, weights_out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_gmm_epilogue_scatter(const int32_t* symbols, const long long* bitmap, int C, int64_t HW,
+                                        float* y_hat, cudaStream_t st) {
+    if (C <= 0 || HW <= 0) return cudaSuccess;
+    gmm_epilogue_scatter_kernel<<<C, kPrThreads, 0, st>>>(symbols, bitmap, HW, y_hat);
+    return cudaGetLastError();
+}
+
+float gmm_extremum_from_bits(uint32_t code) {
+    const uint32_t b = (code & 0x80000000u) ? (code & 0x7fffffffu) : ~code;
+    float f;
+    memcpy(&f, &b, 4);
+    return f;
+}
+
+}  // namespace flashgmm

@@ -21,6 +21,8 @@ Deliberate differences: tensors must be CUDA float32 (there is no CPU fallback);
 """
 from __future__ import annotations
 
+import ctypes as C
+
 from typing import Any, List, Optional, Tuple, Union
 
 import torch
@@ -271,21 +273,47 @@ class GaussianMixtureConditional(nn.Module):
     y_q = None
     y_p = None
 
+    # -- compress / decompress glue on the device (csrc/gmm_prologue.cu) ------------------
+    def _kept_planes(self, y_q, scales, means, weights, bitmap, n_kept):
+        """Kept channels' symbols (int32) and parameters as (Nsym, K) views with strides (1, Nsym):
+        what reshape_entropy_parameters + the channel compaction of entropy_models.py:846 produce,
+        in one launch."""
+        C_, HW = bitmap.numel(), scales.size(2) * scales.size(3)
+        n_sym = n_kept * HW
+        dev = scales.device
+        sym = torch.empty(n_sym, dtype=torch.int32, device=dev) if y_q is not None else None
+        planes = [torch.empty((self.K, n_sym), dtype=torch.float32, device=dev) for _ in range(3)]
+        sc, mu, w = (t.contiguous() for t in (scales, means, weights))
+        _lib.check(_lib.lib().flashgmm_gmm_prologue_gather(
+            _lib.ctx(dev.index or 0), y_q.data_ptr() if y_q is not None else None, sc.data_ptr(), mu.data_ptr(),
+            w.data_ptr(), bitmap.data_ptr(), C_, HW, self.K, n_sym, sym.data_ptr() if sym is not None else None,
+            planes[0].data_ptr(), planes[1].data_ptr(), planes[2].data_ptr(),
+            torch.cuda.current_stream(dev).cuda_stream))
+        return sym, planes[0].t(), planes[1].t(), planes[2].t()
+
     # -- entropy_models.py:833-867 -------------------------------------------------------
     def compress(self, y, scales, means, weights):
         _require_cuda_f32(y, scales, means, weights)
         if self.K != 4:
             raise ValueError("the GMM rANS coder binds K=4 only (rans_interface.cpp:60, 982)")
-        # abs_max from the UNROUNDED y, truncated like .int() (entropy_models.py:834-837); one sync
-        hi, lo = torch.stack((y.max(), y.min())).abs().int().tolist()
-        abs_max = max(hi, lo) + 1
+        if y.size(0) != 1:
+            raise ValueError("compress takes one image at a time (the reference squeezes the batch axis, entropy_models.py:842)")
+        dev = y.device
+        C_, HW = y.size(1), y.size(2) * y.size(3)
+        y = y.contiguous()
+        y_quantized = torch.empty_like(y)
+        zero_bitmap = torch.empty(C_, dtype=torch.int64, device=dev)
+        bitmap_h = (C.c_int32 * max(1, C_))()
+        y_max, y_min = C.c_float(), C.c_float()
+        # one kernel + one synchronisation: round, zero bitmap, extrema of the UNROUNDED y
+        _lib.check(_lib.lib().flashgmm_gmm_prologue_scan(
+            _lib.ctx(dev.index or 0), y.data_ptr(), C_, HW, y_quantized.data_ptr(), zero_bitmap.data_ptr(), bitmap_h,
+            C.byref(y_max), C.byref(y_min), torch.cuda.current_stream(dev).cuda_stream))
+        # abs_max truncated like .abs().int() (entropy_models.py:834-837)
+        abs_max = max(int(abs(y_max.value)), int(abs(y_min.value))) + 1
         abs_max = 1 if abs_max < 1 else abs_max
-
-        y_quantized = torch.round(y)
-        zero_bitmap = torch.where(torch.sum(torch.abs(y_quantized), (3, 2)).squeeze(0) == 0, 0, 1)
-        nonzero = torch.nonzero(zero_bitmap).flatten().tolist()
-        symbols = y_quantized[:, nonzero].reshape(-1).int()
-        scales, means, weights = self.reshape_entropy_parameters(scales, means, weights, nonzero)
+        n_kept = sum(1 for i in range(C_) if bitmap_h[i])
+        symbols, scales, means, weights = self._kept_planes(y_quantized, scales, means, weights, zero_bitmap, n_kept)
         if self.y_q is None:
             self.y_q = symbols
         else:
@@ -298,13 +326,18 @@ class GaussianMixtureConditional(nn.Module):
         _require_cuda_f32(scales, means, weights)
         if self.K != 4:
             raise ValueError("the GMM rANS coder binds K=4 only (rans_interface.cpp:60, 982)")
-        nonzero = torch.nonzero(zero_bitmap).flatten().tolist()
-        scales_ = scales
-        scales, means, weights = self.reshape_entropy_parameters(scales, means, weights, nonzero)
-        symbols = self.entropy_coder._decoder.decode_with_indexes_gmm(strings, scales, means, weights, abs_max + 1)
+        if scales.size(0) != 1:
+            raise ValueError("decompress takes one image at a time (entropy_models.py:842, 905)")
+        dev = scales.device
+        bitmap = zero_bitmap.to(device=dev, dtype=torch.int64).contiguous()
+        C_, HW = bitmap.numel(), scales.size(2) * scales.size(3)
+        n_kept = int(torch.count_nonzero(bitmap).item())               # the one sync of this call
+        _sym, sc, mu, w = self._kept_planes(None, scales, means, weights, bitmap, n_kept)
+        symbols = self.entropy_coder._decoder.decode_with_indexes_gmm(strings, sc, mu, w, abs_max + 1)
         self.y_q = None
-        symbols = symbols.reshape(scales_.size(0), -1, scales_.size(2), scales_.size(3))
-        y_hat = torch.zeros(scales_.size(0), zero_bitmap.size(0), scales_.size(2), scales_.size(3),
-                            device=scales_.device)
-        y_hat[:, nonzero] = symbols.float()
+        symbols = symbols.to(device=dev, dtype=torch.int32).contiguous()
+        y_hat = torch.empty(1, C_, scales.size(2), scales.size(3), device=dev)
+        _lib.check(_lib.lib().flashgmm_gmm_epilogue_scatter(
+            _lib.ctx(dev.index or 0), symbols.data_ptr() if symbols.numel() else None, bitmap.data_ptr(), C_, HW,
+            y_hat.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
         return y_hat

@@ -177,6 +177,33 @@ int flashgmm_gmm_likelihood_bwd(flashgmm_ctx* ctx, const float* y_d, const float
                                 float* grad_y_d, float* grad_scales_d, float* grad_means_d,
                                 float* grad_weights_d, void* stream);
 
+/* ---- GaussianMixtureConditional.compress / decompress glue on the device ----
+ * EM = compressai/entropy_models/entropy_models.py. Layouts are the reference's: y (1, C, H, W)
+ * contiguous, parameters (1, K*C, H, W) contiguous (component k of channel c at channel k*C + c),
+ * HW = H*W. All pointers are device pointers unless named _h. */
+
+/* EM:834-845: y_quantized = round(y); zero bitmap (1 = the channel has a nonzero symbol), as int64
+ * on the device (bitmap_out_d, may be NULL) and as int32 on the host; max and min of the UNROUNDED
+ * y (y_max_h, y_min_h; the caller forms abs_max as EM:834-837 does). One kernel, one small copy,
+ * one synchronisation of `stream`. */
+int flashgmm_gmm_prologue_scan(flashgmm_ctx* ctx, const float* y_d, int64_t C, int64_t HW,
+                               float* y_quantized_out_d, int64_t* bitmap_out_d, int32_t* bitmap_out_h,
+                               float* y_max_h, float* y_min_h, void* stream);
+
+/* EM:846-847 + reshape_entropy_parameters EM:810-828: the kept channels' symbols as int32 and
+ * their parameters as K-major planes [K][n_sym] (n_sym = kept channels * HW; scales clamped to
+ * [0.11, 256]) -- the (n_sym, K) views with strides (1, n_sym) the coder reads. y_quantized_d and
+ * symbols_out_d may both be NULL (decompress needs the parameters only). Asynchronous on `stream`. */
+int flashgmm_gmm_prologue_gather(flashgmm_ctx* ctx, const float* y_quantized_d, const float* scales_d,
+                                 const float* means_d, const float* weights_d, const int64_t* bitmap_d,
+                                 int64_t C, int64_t HW, int K, int64_t n_sym, int32_t* symbols_out_d,
+                                 float* scales_out_d, float* means_out_d, float* weights_out_d, void* stream);
+
+/* EM:902-909: y_hat (1, C, H, W) = decoded symbols of the kept channels as float, zeros elsewhere.
+ * Asynchronous on `stream`. */
+int flashgmm_gmm_epilogue_scatter(flashgmm_ctx* ctx, const int32_t* symbols_d, const int64_t* bitmap_d,
+                                  int64_t C, int64_t HW, float* y_hat_out_d, void* stream);
+
 /* ---- host-only halves (no GPU): the serial rANS recurrence ---- */
 
 /* Push packed (start|freq<<16, freq==0 = bypass -> needs symbols[i]) records:

@@ -201,3 +201,43 @@ def test_state_dict_keys_match_reference():
     assert sorted(fg.GaussianMixtureConditional(K=4).state_dict().keys()) == sorted(want)
     codec = fg.GaussianMixtureConditionalLatentCodec(K=4)
     assert sorted(codec.state_dict().keys()) == sorted("gaussian_mixture_conditional." + k for k in want)
+
+
+# ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape", [(1, 7, 5, 3), (1, 64, 16, 24), (1, 320, 32, 48), (1, 1, 1, 1)])
+def test_compress_glue_kernels_match_the_tensor_ops(shape):
+    """csrc/gmm_prologue.cu against the reference's own tensor ops (entropy_models.py:810-851, 902-909):
+    abs_max, y_quantized, zero bitmap, compacted symbols, K-major parameter views, scatter back."""
+    _B, Cc, H, W = shape
+    g = torch.Generator().manual_seed(sum(shape))
+    y = (torch.randn(shape, generator=g) * 3).cuda()
+    y[:, ::3] *= 0.05                                   # channels that round to all zeros
+    y[0, -1, 0, 0] = -17.6                              # the extremum is negative
+    sc = (torch.rand((1, 4 * Cc, H, W), generator=g) * 3 + 0.05).cuda()      # some below the 0.11 clamp
+    mu = torch.randn((1, 4 * Cc, H, W), generator=g).cuda()
+    w = torch.softmax(torch.randn((1, 4, Cc, H, W), generator=g), 1).reshape(1, 4 * Cc, H, W).cuda()
+    m = fg.GaussianMixtureConditional(K=4).cuda()
+
+    # the reference's ops
+    hi, lo = torch.stack((y.max(), y.min())).abs().int().tolist()
+    want_abs_max = max(max(hi, lo) + 1, 1)
+    yq = torch.round(y)
+    want_bitmap = torch.where(torch.sum(torch.abs(yq), (3, 2)).squeeze(0) == 0, 0, 1)
+    nz = torch.nonzero(want_bitmap).flatten().tolist()
+    want_sym = yq[:, nz].reshape(-1).int()
+    want_sc, want_mu, want_w = m.reshape_entropy_parameters(sc, mu, w, nz)
+
+    (bts, abs_max, bitmap), y_q = m.compress(y, sc, mu, w)
+    assert abs_max == want_abs_max
+    assert bitmap.dtype == torch.int64 and torch.equal(bitmap, want_bitmap)
+    assert torch.equal(y_q, yq)
+    assert torch.equal(m.y_q, want_sym)
+    sym, a, b, c = m._kept_planes(yq, sc, mu, w, want_bitmap, len(nz))
+    assert torch.equal(sym, want_sym)
+    for got, want in ((a, want_sc), (b, want_mu), (c, want_w)):
+        assert got.shape == want.shape and got.stride() == (1, got.shape[0]) and torch.equal(got, want)
+    # same bytes as the coder fed with the reference's tensors, and the round trip
+    assert bts == ans.RansEncoder().encode_with_indexes_gmm(want_sym, want_sc, want_mu, want_w, abs_max + 1)
+    m2 = fg.GaussianMixtureConditional(K=4).cuda()
+    y_hat = m2.decompress(bts, abs_max, bitmap.cpu(), sc, mu, w)      # bitmap may arrive on the CPU
+    assert y_hat.shape == y.shape and torch.equal(y_hat, yq)
