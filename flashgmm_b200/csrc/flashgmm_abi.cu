@@ -202,7 +202,8 @@ struct DevDecode {
     std::vector<cudaEvent_t> ev_rows, ev_pop, ev_up;      // one per chunk (grown on demand)
     std::vector<cudaEvent_t> t0, t1;                      // kernel timing pairs (profiling only)
     cudaEvent_t ev_words[kPopGroups] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // a group's bitstreams are up
-    DevBuf rows[kPopGroups][kRowBufs], words, desc, state, params, out;
+    DevBuf rows[kPopGroups][kRowBufs], words, desc, state, params, out, claim;
+    int n_sm = 0;
     PinBuf h_desc, h_words, h_state;
     int init() {
         if (st_rows) return FLASHGMM_OK;
@@ -243,7 +244,7 @@ struct DevDecode {
         if (st_words) cudaStreamDestroy(st_words);
         st_rows = st_copy = st_words = nullptr;
         for (auto& gr : rows) for (auto& r : gr) r.release();
-        words.release(); desc.release(); state.release();
+        words.release(); desc.release(); state.release(); claim.release();
         params.release(); out.release(); h_desc.release(); h_words.release(); h_state.release();
     }
 };
@@ -253,7 +254,8 @@ struct DevEncode {
     cudaStream_t st = nullptr;
     cudaEvent_t t[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_sf = nullptr;          // the device part's CDF pass is done (its inputs have crossed PCIe)
-    DevBuf packed, scratch, desc, rcp, result;
+    DevBuf packed, scratch, desc, rcp, result, out_d, result_d;
+    bool out_on_device = false;
     PinBuf h_desc, h_result, h_out;
     bool rcp_ready = false;
     // a batch in flight between encode_batch_device_begin and _finish
@@ -273,7 +275,7 @@ struct DevEncode {
         for (auto& e : t) if (e) { cudaEventDestroy(e); e = nullptr; }
         if (ev_sf) { cudaEventDestroy(ev_sf); ev_sf = nullptr; }
         st = nullptr; rcp_ready = false;
-        packed.release(); scratch.release(); desc.release(); rcp.release(); result.release();
+        packed.release(); scratch.release(); desc.release(); rcp.release(); result.release(); out_d.release(); result_d.release();
         h_desc.release(); h_result.release(); h_out.release();
     }
 };
@@ -777,6 +779,9 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
             if (items[c].g == g) { biggest = std::max(biggest, item_bytes(g, items[c].lo, items[c].hi)); ++n_items; }
         for (int b = 0; b < std::min(n_items, kRowBufs); ++b) CU_TRY(D.rows[g][b].need((size_t)biggest));
     }
+    static const bool spread = env_long("FLASHGMM_POP_SPREAD", 0) != 0;     // SM-aware placement of the pop warps (opt-in: spreads them, measured no gain)
+    if (D.n_sm == 0) { CU_TRY(cudaDeviceGetAttribute(&D.n_sm, cudaDevAttrMultiProcessorCount, ctx->device)); D.n_sm = std::max(1, D.n_sm); }
+    if (spread) CU_TRY(D.claim.need((size_t)nch * kPopClaimInts * sizeof(int)));
     CU_TRY(D.words.need(total_words * 4 + 16));
     CU_TRY(D.h_words.need(total_words * 4 + 16));
     CU_TRY(D.state.need((size_t)na * 16));
@@ -891,7 +896,9 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
         CU_TRY(cudaStreamWaitEvent(sp, D.ev_rows[c], 0));
         if (items[c].lo == 0) CU_TRY(cudaStreamWaitEvent(sp, D.ev_words[items[c].g], 0));
         if (prof) CU_TRY(cudaEventRecord(D.t0[2 * c + 1], sp));
-        CU_TRY(launch_gmm_pop_rows(d_pd + ci[c].first, ci[c].count, lane_slots, mode, sp));
+        CU_TRY(launch_gmm_pop_rows(d_pd + ci[c].first, ci[c].count, lane_slots, mode,
+                                   spread ? static_cast<int*>(D.claim.p) + (size_t)c * kPopClaimInts : nullptr,
+                                   (ci[c].count + D.n_sm - 1) / D.n_sm, sp));
         if (prof) CU_TRY(cudaEventRecord(D.t1[2 * c + 1], sp));
         CU_TRY(cudaEventRecord(D.ev_pop[c], sp));
         if (items[c].hi >= streams[act[grp_begin[items[c].g]]].n) {
@@ -916,6 +923,7 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     if ((rc = upload_chunk(0))) return rc;
     if ((rc = launch_rows(0))) return rc;
     {
+        if (spread) CU_TRY(cudaMemsetAsync(D.claim.p, 0, (size_t)nch * kPopClaimInts * sizeof(int), D.st_words));
         // group by group, the longest streams' words first: their pop is the critical path
         uint32_t* hw = static_cast<uint32_t*>(D.h_words.p);
         for (int g = 0; g < ng; ++g) {
@@ -981,9 +989,18 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
         }
     }
     const uint64_t* hs = static_cast<const uint64_t*>(D.h_state.p);
+    if (prof && trace) {                                     // how the groups' last pop launches were spread over the SMs
+        for (int g2 = 0; g2 < ng; ++g2) {
+            int per_sm[1024] = {0}, used = 0, worst_sm = 0;
+            for (int a = grp_begin[g2]; a < grp_begin[g2 + 1]; ++a) ++per_sm[(hs[2 * a + 1] >> 40) & 1023];
+            for (int v : per_sm) { used += v ? 1 : 0; worst_sm = std::max(worst_sm, v); }
+            fprintf(stderr, "[flashgmm trace] group %d: %d pop warps on %d SMs, at most %d on one SM\n", g2,
+                    grp_begin[g2 + 1] - grp_begin[g2], used, worst_sm);
+        }
+    }
     for (int a = 0; a < na; ++a) {
         flashgmm_stream& s = streams[act[a]];
-        if ((hs[2 * a + 1] >> 32) != 0) {
+        if (((hs[2 * a + 1] >> 32) & 1u) != 0) {
             s.status = fail(FLASHGMM_ETRUNC, "bitstream truncated: decoder read past %zu bytes", s.bytes_cap);
             worst = s.status;
         }
@@ -1064,6 +1081,12 @@ int encode_batch_device_begin(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     CU_TRY(E.h_out.need(sc_total * 4 + 16));
     CU_TRY(E.result.need(16));
     CU_TRY(E.h_result.need((size_t)na * 32 + 16));
+    static const bool out_dev = env_long("FLASHGMM_PUSH_OUT_DEVICE", 0) != 0;
+    E.out_on_device = out_dev;
+    if (out_dev) {
+        CU_TRY(E.out_d.need(sc_total * 4 + 16));
+        CU_TRY(E.result_d.need((size_t)na * 32 + 16));
+    }
     const size_t sf_bytes = ((size_t)na * sizeof(SfDesc) + 15) / 16 * 16;
     CU_TRY(E.desc.need(sf_bytes + (size_t)na * sizeof(PushDesc)));
     CU_TRY(E.h_desc.need(sf_bytes + (size_t)na * sizeof(PushDesc)));
@@ -1076,7 +1099,7 @@ int encode_batch_device_begin(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     SfDesc* h_sf = static_cast<SfDesc*>(E.h_desc.p);
     PushDesc* h_pd = reinterpret_cast<PushDesc*>(static_cast<char*>(E.h_desc.p) + sf_bytes);
     uint32_t* d_packed = static_cast<uint32_t*>(E.packed.p);
-    uint32_t* d_result = static_cast<uint32_t*>(E.h_result.p);
+    uint32_t* d_result = static_cast<uint32_t*>(E.out_on_device ? E.result_d.p : E.h_result.p);
     unsigned long long* d_used = static_cast<unsigned long long*>(E.result.p);
     double total_n = 0;
     for (int a = 0; a < na; ++a) {
@@ -1088,7 +1111,7 @@ int encode_batch_device_begin(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
         total_n += (double)s.n;
     }
     CU_TRY(cudaMemcpyAsync(E.desc.p, E.h_desc.p, sf_bytes + (size_t)na * sizeof(PushDesc), cudaMemcpyHostToDevice, E.st));
-    CU_TRY(cudaMemsetAsync(d_used, 0, 8, E.st));
+    CU_TRY(cudaMemsetAsync(d_used, 0, 16, E.st));                  // words claimed (u64) + push warps resident (u32)
     const bool prof = E.prof = g_prof_on.load(std::memory_order_relaxed) != 0;
     E.total_n = total_n;
     if (prof) CU_TRY(cudaEventRecord(E.t[0], E.st));
@@ -1096,7 +1119,8 @@ int encode_batch_device_begin(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     if (prof) CU_TRY(cudaEventRecord(E.t[1], E.st));
     CU_TRY(cudaEventRecord(E.ev_sf, E.st));
     CU_TRY(launch_gmm_push(reinterpret_cast<const PushDesc*>(static_cast<char*>(E.desc.p) + sf_bytes), na,
-                           static_cast<const PushRcp*>(E.rcp.p), static_cast<uint32_t*>(E.h_out.p), d_used, E.st));
+                           static_cast<const PushRcp*>(E.rcp.p), static_cast<uint32_t*>(E.out_on_device ? E.out_d.p : E.h_out.p), d_used,
+                           reinterpret_cast<unsigned int*>(d_used + 1), E.st));
     g_launches.fetch_add(2, std::memory_order_relaxed);
     return FLASHGMM_OK;
 }
@@ -1110,6 +1134,15 @@ int encode_batch_device_finish(flashgmm_ctx* ctx, flashgmm_stream* streams) {
     const bool prof = E.prof;
     const double total_n = E.total_n;
     CU_TRY(cudaStreamSynchronize(E.st));
+    if (E.out_on_device) {
+        CU_TRY(cudaMemcpyAsync(E.h_result.p, E.result_d.p, (size_t)na * 32, cudaMemcpyDeviceToHost, E.st));
+        CU_TRY(cudaStreamSynchronize(E.st));
+        unsigned long long tot = 0;
+        const uint32_t* r = static_cast<const uint32_t*>(E.h_result.p);
+        for (int a = 0; a < na; ++a) tot += std::min<unsigned long long>(r[8 * a], streams[act[a]].bytes_cap / 4);
+        if (tot) CU_TRY(cudaMemcpyAsync(E.h_out.p, E.out_d.p, (size_t)tot * 4, cudaMemcpyDeviceToHost, E.st));
+        CU_TRY(cudaStreamSynchronize(E.st));
+    }
     const uint32_t* hr = static_cast<const uint32_t*>(E.h_result.p);
     unsigned long long used_words = 0;
     unsigned long long t_first = ~0ull, t_last = 0;
@@ -1127,8 +1160,14 @@ int encode_batch_device_finish(flashgmm_ctx* ctx, flashgmm_stream* streams) {
             latest_start = std::max(latest_start, b - t_first);
             longest = std::max(longest, e - b);
         }
-        fprintf(stderr, "[flashgmm trace] push kernel ran %.3f ms (its own %%globaltimer stamps): last warp started at %.3f ms, longest warp %.3f ms\n",
+        fprintf(stderr, "[flashgmm trace] push kernel ran %.3f ms (its own %%globaltimer stamps): last warp started at %.3f ms, longest warp %.3f ms;",
                 (double)(t_last - t_first) * 1e-6, (double)latest_start * 1e-6, (double)longest * 1e-6);
+        for (int a : {0, na / 4, na / 2, 3 * na / 4, na - 1}) {
+            const unsigned long long b = (unsigned long long)hr[8 * a + 4] | ((unsigned long long)hr[8 * a + 5] << 32);
+            const unsigned long long e = (unsigned long long)hr[8 * a + 6] | ((unsigned long long)hr[8 * a + 7] << 32);
+            fprintf(stderr, " n=%lld: %.3f-%.3f", (long long)streams[act[a]].n, (double)(b - t_first) * 1e-6, (double)(e - t_first) * 1e-6);
+        }
+        fprintf(stderr, "\n");
     }
     if (prof) {
         float a = 0;
@@ -1158,12 +1197,16 @@ int encode_batch_device_finish(flashgmm_ctx* ctx, flashgmm_stream* streams) {
 // to the worker threads, the rest to the device, both at once: k minimises the later finish.
 // (One free box: the long streams stay on the host, the many short ones go to the GPU. Several
 // ranks sharing few cores: most or all of the batch goes to the GPU.)
-int plan_push_split(const flashgmm_ctx* ctx, const flashgmm_stream* streams, int n_streams, std::vector<int>* order) {
+int plan_push_split(const flashgmm_ctx* ctx, const flashgmm_stream* streams, int n_streams, int mem, std::vector<int>* order) {
     order->resize(n_streams);
     for (int i = 0; i < n_streams; ++i) (*order)[i] = i;
     std::sort(order->begin(), order->end(), [&](int a, int b) { return streams[a].n > streams[b].n; });
     if (ctx->push_policy == 1 || n_streams < 4) return n_streams;
     if (ctx->push_policy == 2) return 0;
+    // page-locked host inputs: the call is bound by PCIe (52 B per symbol), and >= 6 workers push
+    // faster than the link delivers; a device part only adds its push as a tail (measured 14.4 ms
+    // split against 12.7 ms all-host for 24 images)
+    if (mem == FLASHGMM_MEM_HOST && ctx->n_workers >= 6) return n_streams;
     const double workers = (double)std::max(1, ctx->n_workers);
     double best = 1e300, host_sum = 0;
     int best_k = n_streams;
@@ -1230,9 +1273,11 @@ int run_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mo
 // page-locked host memory; the workers take (wave, stream) tasks in wave-major order and push each
 // as soon as its wave's event has fired and the stream's previous wave is done. PCIe (or the FP32
 // pipe) never waits for a push, and a worker makes no CUDA call per task beyond the event wait.
-// `gate` (optional): an event the first wave waits for (the device part of a split batch goes first).
+// `gate` (optional): an event the first wave waits for (the device part of a split batch goes first);
+// `wait_ctr` (optional): a device counter the first wave waits for on the device (>= wait_target).
 // Returns -1 when the batch is not eligible (pageable host tensors), before touching anything.
-int encode_batch_waves(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem, cudaEvent_t gate) {
+int encode_batch_waves(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem, cudaEvent_t gate,
+                       const unsigned int* wait_ctr, unsigned int wait_target) {
     std::lock_guard<std::mutex> g(ctx->mu);
     CU_TRY(cudaSetDevice(ctx->device));
     if (!ctx->hw) ctx->hw.reset(new HostWaves());
@@ -1318,8 +1363,11 @@ int encode_batch_waves(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_stream
         wave_blocks[w] = blocks;
     }
     CU_TRY(cudaMemcpyAsync(H.desc.p, H.h_desc.p, (size_t)nt * sizeof(SfDesc), cudaMemcpyHostToDevice, H.st));
-    CU_TRY(cudaMemsetAsync(d_packed, 0, pk_total * 4, H.st));      // clears the bypass flags (HBM speed: microseconds)
+    CU_TRY(launch_gmm_sf_clear_flags(static_cast<const SfDesc*>(H.desc.p), nt, H.st));   // the tasks' bypass tails start empty
     if (gate) CU_TRY(cudaStreamWaitEvent(H.st, gate, 0));
+    // the wide kernels below must not start while the device part's one-warp push CTAs are being
+    // placed (gmm_push.cu::gmm_wait_started_kernel)
+    if (wait_ctr) CU_TRY(launch_gmm_wait_started(wait_ctr, wait_target, H.st));
     for (int w = 0; w < nw_waves; ++w) {
         if (prof) CU_TRY(cudaEventRecord(H.t0[w], H.st));
         CU_TRY(launch_gmm_startfreq_batched(static_cast<const SfDesc*>(H.desc.p) + wave_first[w],
@@ -1605,13 +1653,14 @@ int flashgmm_gmm_encode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
     if (n_streams < 0 || (n_streams > 0 && !streams)) return fail(FLASHGMM_EINVAL, "bad stream array");
     std::vector<int> order;
-    const int k_host = plan_push_split(ctx, streams, n_streams, &order);
+    const int k_host = plan_push_split(ctx, streams, n_streams, mem, &order);
     static const bool waves = env_long("FLASHGMM_ENC_WAVES", 1) != 0;
     // host part: batched CDF waves + worker pushes; falls back to one kernel per stream chunk for
     // pageable host tensors (-1) or when switched off
-    auto host_encode = [&](flashgmm_stream* part, int n_part, cudaEvent_t gate) -> int {
+    auto host_encode = [&](flashgmm_stream* part, int n_part, cudaEvent_t gate, const unsigned int* wait_ctr = nullptr,
+                           unsigned int wait_target = 0) -> int {
         if (waves && n_part >= 2) {
-            const int rc = encode_batch_waves(ctx, part, n_part, mode, mem, gate);
+            const int rc = encode_batch_waves(ctx, part, n_part, mode, mem, gate, wait_ctr, wait_target);
             if (rc != -1) return rc;
         }
         return run_batch(ctx, part, n_part, mode, mem, encode_stream);
@@ -1634,7 +1683,13 @@ int flashgmm_gmm_encode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     // host inputs: the device part's parameters cross PCIe first (its push then runs while the host
     // part's cross), instead of both halving the link
     cudaEvent_t gate = (dev_queued && mem == FLASHGMM_MEM_HOST && !ctx->de->act.empty()) ? ctx->de->ev_sf : nullptr;
-    int host_rc = host_part.empty() ? FLASHGMM_OK : host_encode(host_part.data(), (int)host_part.size(), gate);
+    // ... and its startfreq kernel always does (event), then its push warps are placed (device counter)
+    const bool dev_live = dev_queued && !ctx->de->act.empty();
+    if (dev_live) gate = ctx->de->ev_sf;
+    const unsigned int* wait_ctr = dev_live ? reinterpret_cast<const unsigned int*>(static_cast<const unsigned long long*>(ctx->de->result.p) + 1) : nullptr;
+    int host_rc = host_part.empty() ? FLASHGMM_OK
+                                    : host_encode(host_part.data(), (int)host_part.size(), gate, wait_ctr,
+                                                  dev_live ? (unsigned int)ctx->de->act.size() : 0u);
     const double bt_host = bms();
     if (dev_queued) {
         const std::string host_err = host_rc ? g_err : std::string();

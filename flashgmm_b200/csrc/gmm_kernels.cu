@@ -371,6 +371,20 @@ gmm_startfreq_batched_kernel(const SfDesc* __restrict__ descs, int n_desc) {
     }
 }
 
+namespace {
+__global__ void gmm_sf_clear_flags_kernel(const SfDesc* __restrict__ descs, int n_desc) {
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i < n_desc && descs[i].flag != nullptr) descs[i].flag[threadIdx.x & 31] = 0u;
+}
+}  // namespace
+
+// zeroes the 32-word bypass tail of every descriptor that has one (before the launches that fill them)
+cudaError_t launch_gmm_sf_clear_flags(const SfDesc* descs_d, int n_desc, cudaStream_t st) {
+    if (n_desc <= 0) return cudaSuccess;
+    gmm_sf_clear_flags_kernel<<<(n_desc + 7) / 8, 256, 0, st>>>(descs_d, n_desc);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_gmm_startfreq_batched(const SfDesc* descs_d, int n_desc, int total_blocks, int mode, cudaStream_t st) {
     if (n_desc <= 0 || total_blocks <= 0) return cudaSuccess;
     switch (mode) {

@@ -66,7 +66,11 @@ inline int gmm_pop_lane_slots(int max_R) {             // 1, 2 or 4 intervals pe
 // 32 / 64 / 128: lane-row records.
 cudaError_t launch_gmm_cdf_rows_batched(const RowsDesc* descs_d, int n_desc, int total_blocks, int S,
                                         int max_row_words, int lane_slots, int mode, cudaStream_t st);
-cudaError_t launch_gmm_pop_rows(const PopDesc* descs_d, int n_desc, int lane_slots, int mode, cudaStream_t st);
+// claim: 1025 zeroed ints per launch (next stream, streams taken per SM) or NULL (CTA i = stream i);
+// quota: streams one SM may take
+constexpr int kPopClaimInts = 1025;
+cudaError_t launch_gmm_pop_rows(const PopDesc* descs_d, int n_desc, int lane_slots, int mode, int* claim, int quota,
+                                cudaStream_t st);
 
 // ---- device-resident encode: batched startfreq + one-warp-per-stream push (gmm_push.cu) ----
 constexpr int kSfBypassSlots = 15;
@@ -80,6 +84,7 @@ struct SfDesc {
                               // [1 + 2j], [2 + 2j] = index and symbol value of the j-th (first kSfBypassSlots only)
 };
 cudaError_t launch_gmm_startfreq_batched(const SfDesc* descs_d, int n_desc, int total_blocks, int mode, cudaStream_t st);
+cudaError_t launch_gmm_sf_clear_flags(const SfDesc* descs_d, int n_desc, cudaStream_t st);
 
 // Exact reciprocal of every 16-bit frequency: q = (umul64hi(x, rcp) >> shift) == x / freq for
 // x < 2^63 (rans_host.hpp::RcpEntry, built on the host, uploaded once per ctx).
@@ -95,7 +100,9 @@ struct PushDesc {
 // All streams' words end up back to back in `out` (claimed with one atomicAdd per stream on
 // *out_used, in words); result[1] says where.
 cudaError_t launch_gmm_push(const PushDesc* descs_d, int n_desc, const PushRcp* rcp_d, uint32_t* out,
-                            unsigned long long* out_used, cudaStream_t st);
+                            unsigned long long* out_used, unsigned int* started, cudaStream_t st);
+// blocks `st` on the device until *started >= target (every push warp resident) or 3 ms have passed
+cudaError_t launch_gmm_wait_started(const unsigned int* started, unsigned int target, cudaStream_t st);
 
 // Interleaved multi-lane rANS (gmm_ileave.cu). scratch: n_seg * gmm_ileave_scratch_words()
 // uint16; seg_words: n_seg uint32; out: device buffer for the whole container.

@@ -188,7 +188,7 @@ struct Ival { uint32_t lo, wd; };
 //                 intervals that hold the most mass -- one LDS.64 and no unpacking per symbol.
 template <int NI, bool WIN>
 __global__ void __launch_bounds__(32)
-gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
+gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode, int n_desc, int quota, int* __restrict__ claim) {
     extern __shared__ __align__(128) uint8_t ring[];
     __shared__ uint64_t bars[kPopStages];
     __shared__ __align__(16) uint32_t bcast[4];
@@ -201,9 +201,37 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
     constexpr int kGroup = (kPopStageBytes / kRowBytes) >= 32 ? 32 : 16;
     constexpr int kRps = kGroup;
 
-    const PopDesc d = descs[blockIdx.x];
-    if (d.n <= 0) return;
     const int lane = threadIdx.x;
+    // Which stream is this CTA's? One-warp CTAs must be SPREAD over the SMs (a warp of this kernel
+    // uses about a third of a sub-partition's issue slots; six on one SM run far slower each), but
+    // while the rows kernels keep every SM nearly full the block scheduler drops a launch's CTAs
+    // onto the few SMs that have room at that instant (measured: 48 warps on 8 SMs). So the grid is
+    // several times the number of streams and a CTA only takes a stream if its SM is below its
+    // quota of them; otherwise it lingers a few microseconds (keeping the slot busy, so that the
+    // CTAs behind it go elsewhere) and leaves. The grid's last n_desc CTAs take whatever is left.
+    int idx = (int)blockIdx.x;
+    if (claim != nullptr) {
+        int got = -1;
+        bool linger = false;
+        if (lane == 0 && *reinterpret_cast<volatile int*>(claim) < n_desc) {
+            uint32_t smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            int* cnt = claim + 1 + (smid & 1023u);
+            const bool last_resort = (int)blockIdx.x >= (int)gridDim.x - n_desc;
+            if (atomicAdd(cnt, 1) < quota || last_resort) {
+                got = atomicAdd(claim, 1);
+                if (got >= n_desc) got = -1;
+            } else {
+                atomicSub(cnt, 1);
+                linger = true;
+            }
+        }
+        if (linger) __nanosleep(4000);
+        idx = __shfl_sync(kFull, got, 0);
+        if (idx < 0) return;
+    }
+    const PopDesc d = descs[idx];
+    if (d.n <= 0) return;
     const int R = d.R;
     const int n_stages = (d.n + kRps - 1) / kRps;
     const uint8_t* src = reinterpret_cast<const uint8_t*>(d.rows);
@@ -232,7 +260,7 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
         S.xlo = (uint32_t)d.state[0]; S.xhi = (uint32_t)(d.state[0] >> 32);
         S.ptr = (uint32_t)d.state[1];
     }
-    const uint32_t sticky_overrun = d.first ? (d.n_words < 2 ? 1u : 0u) : (uint32_t)(d.state[1] >> 32);
+    const uint32_t sticky_overrun = d.first ? (d.n_words < 2 ? 1u : 0u) : (uint32_t)(d.state[1] >> 32) & 1u;
 
     // word window: blocks [next_blk - 4, next_blk) of 32 words are in win[]; a group needs the
     // words [ptr, ptr + kGroup] and blocks are fetched two ahead of that
@@ -402,20 +430,24 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode) {
     }
     if (lane == 0) {
         d.state[0] = ((uint64_t)S.xhi << 32) | S.xlo;
-        d.state[1] = ((uint64_t)(sticky_overrun | (S.overrun() ? 1u : 0u)) << 32) | S.ptr;
+        uint32_t smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));           // bits 40+: where the stream's last launch ran (trace only)
+        d.state[1] = ((uint64_t)smid << 40) | ((uint64_t)(sticky_overrun | (S.overrun() ? 1u : 0u)) << 32) | S.ptr;
     }
 }
 
 }  // namespace
 
-cudaError_t launch_gmm_pop_rows(const PopDesc* descs_d, int n_desc, int lane_slots, int mode, cudaStream_t st) {
+cudaError_t launch_gmm_pop_rows(const PopDesc* descs_d, int n_desc, int lane_slots, int mode, int* claim, int quota,
+                                cudaStream_t st) {
     if (n_desc <= 0) return cudaSuccess;
     const size_t smem = (size_t)kPopStages * kPopStageBytes;
+    const int grid = claim ? 4 * n_desc : n_desc;             // see the kernel's first lines
     switch (lane_slots) {
-    case kPopWindowed: gmm_pop_rows_kernel<1, true><<<n_desc, 32, smem, st>>>(descs_d, mode); break;
-    case 32: gmm_pop_rows_kernel<1, false><<<n_desc, 32, smem, st>>>(descs_d, mode); break;
-    case 64: gmm_pop_rows_kernel<2, false><<<n_desc, 32, smem, st>>>(descs_d, mode); break;
-    case 128: gmm_pop_rows_kernel<4, false><<<n_desc, 32, smem, st>>>(descs_d, mode); break;
+    case kPopWindowed: gmm_pop_rows_kernel<1, true><<<grid, 32, smem, st>>>(descs_d, mode, n_desc, quota, claim); break;
+    case 32: gmm_pop_rows_kernel<1, false><<<grid, 32, smem, st>>>(descs_d, mode, n_desc, quota, claim); break;
+    case 64: gmm_pop_rows_kernel<2, false><<<grid, 32, smem, st>>>(descs_d, mode, n_desc, quota, claim); break;
+    case 128: gmm_pop_rows_kernel<4, false><<<grid, 32, smem, st>>>(descs_d, mode, n_desc, quota, claim); break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

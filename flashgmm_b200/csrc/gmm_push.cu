@@ -81,11 +81,12 @@ __device__ __forceinline__ void put_symbol(PushState& S, uint32_t* buf, bool lan
 
 __global__ void __launch_bounds__(32)
 gmm_push_kernel(const PushDesc* __restrict__ descs, const PushRcp* __restrict__ rcp_tab,
-                uint32_t* __restrict__ out, unsigned long long* __restrict__ out_used) {
+                uint32_t* __restrict__ out, unsigned long long* __restrict__ out_used, unsigned int* __restrict__ started) {
     __shared__ __align__(16) uint4 park[2][32];      // {rcp.lo, rcp.hi, packed, shift | bias << 16}
 
     const PushDesc d = descs[blockIdx.x];
     const int lane = threadIdx.x;
+    if (lane == 0 && started != nullptr) atomicAdd(started, 1u);      // "this warp is resident": see gmm_wait_started_kernel
     unsigned long long t_begin;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_begin));
     PushState S;
@@ -164,12 +165,35 @@ gmm_push_kernel(const PushDesc* __restrict__ descs, const PushRcp* __restrict__ 
     }
 }
 
+// One-warp CTAs must be SPREAD over the SMs: a warp of this kernel uses about a third of a
+// sub-partition's issue slots, and eight of them on one sub-partition run 2-5x slower each. The
+// block scheduler spreads them when it places them on an idle GPU, but packs them onto whichever
+// SMs free up first when a wide kernel that fills every SM (the startfreq kernels: 16 CTAs x 128
+// threads) is draining at that moment -- measured: the push kernel then takes 10.2 ms instead of
+// 2.2 ms. So the stream that issues such wide kernels beside the push kernel first waits, ON THE
+// DEVICE, until every push warp has reported in. Bounded: gives up after `timeout_ns`.
+__global__ void gmm_wait_started_kernel(const unsigned int* started, unsigned int target, unsigned long long timeout_ns) {
+    if (threadIdx.x != 0) return;
+    unsigned long long t0, t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while (*reinterpret_cast<const volatile unsigned int*>(started) < target) {
+        __nanosleep(500);
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t - t0 > timeout_ns) break;
+    }
+}
+
 }  // namespace
 
 cudaError_t launch_gmm_push(const PushDesc* descs_d, int n_desc, const PushRcp* rcp_d, uint32_t* out,
-                            unsigned long long* out_used, cudaStream_t st) {
+                            unsigned long long* out_used, unsigned int* started, cudaStream_t st) {
     if (n_desc <= 0) return cudaSuccess;
-    gmm_push_kernel<<<n_desc, 32, 0, st>>>(descs_d, rcp_d, out, out_used);
+    gmm_push_kernel<<<n_desc, 32, 0, st>>>(descs_d, rcp_d, out, out_used, started);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_gmm_wait_started(const unsigned int* started, unsigned int target, cudaStream_t st) {
+    gmm_wait_started_kernel<<<1, 32, 0, st>>>(started, target, 3000000ull);      // 3 ms at most
     return cudaGetLastError();
 }
 
