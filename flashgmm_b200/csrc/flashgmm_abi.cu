@@ -254,8 +254,7 @@ struct DevEncode {
     cudaStream_t st = nullptr;
     cudaEvent_t t[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_sf = nullptr;          // the device part's CDF pass is done (its inputs have crossed PCIe)
-    DevBuf packed, scratch, desc, rcp, result, out_d, result_d;
-    bool out_on_device = false;
+    DevBuf packed, scratch, desc, rcp, result;
     PinBuf h_desc, h_result, h_out;
     bool rcp_ready = false;
     // a batch in flight between encode_batch_device_begin and _finish
@@ -275,7 +274,7 @@ struct DevEncode {
         for (auto& e : t) if (e) { cudaEventDestroy(e); e = nullptr; }
         if (ev_sf) { cudaEventDestroy(ev_sf); ev_sf = nullptr; }
         st = nullptr; rcp_ready = false;
-        packed.release(); scratch.release(); desc.release(); rcp.release(); result.release(); out_d.release(); result_d.release();
+        packed.release(); scratch.release(); desc.release(); rcp.release(); result.release();
         h_desc.release(); h_result.release(); h_out.release();
     }
 };
@@ -1081,12 +1080,6 @@ int encode_batch_device_begin(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     CU_TRY(E.h_out.need(sc_total * 4 + 16));
     CU_TRY(E.result.need(16));
     CU_TRY(E.h_result.need((size_t)na * 32 + 16));
-    static const bool out_dev = env_long("FLASHGMM_PUSH_OUT_DEVICE", 0) != 0;
-    E.out_on_device = out_dev;
-    if (out_dev) {
-        CU_TRY(E.out_d.need(sc_total * 4 + 16));
-        CU_TRY(E.result_d.need((size_t)na * 32 + 16));
-    }
     const size_t sf_bytes = ((size_t)na * sizeof(SfDesc) + 15) / 16 * 16;
     CU_TRY(E.desc.need(sf_bytes + (size_t)na * sizeof(PushDesc)));
     CU_TRY(E.h_desc.need(sf_bytes + (size_t)na * sizeof(PushDesc)));
@@ -1099,7 +1092,7 @@ int encode_batch_device_begin(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     SfDesc* h_sf = static_cast<SfDesc*>(E.h_desc.p);
     PushDesc* h_pd = reinterpret_cast<PushDesc*>(static_cast<char*>(E.h_desc.p) + sf_bytes);
     uint32_t* d_packed = static_cast<uint32_t*>(E.packed.p);
-    uint32_t* d_result = static_cast<uint32_t*>(E.out_on_device ? E.result_d.p : E.h_result.p);
+    uint32_t* d_result = static_cast<uint32_t*>(E.h_result.p);
     unsigned long long* d_used = static_cast<unsigned long long*>(E.result.p);
     double total_n = 0;
     for (int a = 0; a < na; ++a) {
@@ -1119,7 +1112,7 @@ int encode_batch_device_begin(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     if (prof) CU_TRY(cudaEventRecord(E.t[1], E.st));
     CU_TRY(cudaEventRecord(E.ev_sf, E.st));
     CU_TRY(launch_gmm_push(reinterpret_cast<const PushDesc*>(static_cast<char*>(E.desc.p) + sf_bytes), na,
-                           static_cast<const PushRcp*>(E.rcp.p), static_cast<uint32_t*>(E.out_on_device ? E.out_d.p : E.h_out.p), d_used,
+                           static_cast<const PushRcp*>(E.rcp.p), static_cast<uint32_t*>(E.h_out.p), d_used,
                            reinterpret_cast<unsigned int*>(d_used + 1), E.st));
     g_launches.fetch_add(2, std::memory_order_relaxed);
     return FLASHGMM_OK;
@@ -1134,15 +1127,6 @@ int encode_batch_device_finish(flashgmm_ctx* ctx, flashgmm_stream* streams) {
     const bool prof = E.prof;
     const double total_n = E.total_n;
     CU_TRY(cudaStreamSynchronize(E.st));
-    if (E.out_on_device) {
-        CU_TRY(cudaMemcpyAsync(E.h_result.p, E.result_d.p, (size_t)na * 32, cudaMemcpyDeviceToHost, E.st));
-        CU_TRY(cudaStreamSynchronize(E.st));
-        unsigned long long tot = 0;
-        const uint32_t* r = static_cast<const uint32_t*>(E.h_result.p);
-        for (int a = 0; a < na; ++a) tot += std::min<unsigned long long>(r[8 * a], streams[act[a]].bytes_cap / 4);
-        if (tot) CU_TRY(cudaMemcpyAsync(E.h_out.p, E.out_d.p, (size_t)tot * 4, cudaMemcpyDeviceToHost, E.st));
-        CU_TRY(cudaStreamSynchronize(E.st));
-    }
     const uint32_t* hr = static_cast<const uint32_t*>(E.h_result.p);
     unsigned long long used_words = 0;
     unsigned long long t_first = ~0ull, t_last = 0;
