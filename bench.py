@@ -158,7 +158,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
 
-    from flashgmm_b200 import _lib, synth
+    from flashgmm_b200 import _lib, shard, synth
     from flashgmm_b200.batch import DecodeJob, EncodeJob
 
     rank = int(os.environ.get("RANK", "0"))
@@ -233,10 +233,7 @@ def run_b200(args):
         barrier()
         # the library's kernels run on its own streams: the step ends when the host call returns,
         # so the wall clock of the synchronous calls is the step time (events on torch's stream agree)
-        t = torch.tensor([max(ms / 1e3, wall)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item()), launches
+        return shard.max_over_ranks(max(ms / 1e3, wall), device=dev), launches
 
     W = max(args.warmup, 3)
     # ---- device-resident arm ----
