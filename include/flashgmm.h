@@ -20,7 +20,9 @@
  *    FLASHGMM_MEM_HOST (page-locked buffers are read by the kernels in place over PCIe,
  *    pageable ones are staged in chunks inside the call) or
  *    FLASHGMM_MEM_DEVICE (used in place on the ctx's device). Bitstreams are
- *    always host memory: the serial rANS state recurrence runs on the host.
+ *    always host memory (they are what leaves the machine); the serial rANS state
+ *    recurrence runs on the host for single streams and on the GPU, one warp per
+ *    stream, for batches (see the batch calls below).
  *  - `mode` is APPROX_MODE with the reference's CODE numbering (RI:98, 223-233):
  *    0 Polya, 1 Abramowitz-Stegun, 2 logistic.
  *  - K is fixed at 4, the only instantiation the reference binds (RI:60, 982).
