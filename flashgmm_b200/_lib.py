@@ -10,10 +10,16 @@ import os
 import threading
 from pathlib import Path
 
-# ~20 CUDA streams are busy at once (worker threads, device encoder / decoder): give each its own
-# hardware queue. Read by the driver when the CUDA context is created; the library's own constructor
-# does the same for non-Python hosts (csrc/flashgmm_abi.cu). A value set by the user wins.
-os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
+
+def want_more_hw_queues(n: int = 32) -> None:
+    """Opt-in (bench.py and standalone tools call it before CUDA is initialised): ~20 CUDA streams are busy at
+    once (worker threads, device encoder / decoder); with the driver's default of 8 hardware queues they share
+    queues and a copy queued behind a long kernel stalls its neighbours. The setting is read when the CUDA
+    context is created, so it has no effect in a process whose context already exists (the library then runs
+    with the default; tests/test_queues_gpu.py covers that configuration). A value set by the user wins."""
+    os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", str(int(n)))
+
 
 PKG = Path(__file__).resolve().parent
 LIB_PATH = PKG / "libflashgmm_b200.so"
@@ -36,6 +42,7 @@ class Stream(C.Structure):
 
 _SIGS = {
     "flashgmm_version": (C.c_int, []),
+    "flashgmm_request_hw_queues": (C.c_int, [C.c_int]),
     "flashgmm_last_error": (C.c_char_p, []),
     "flashgmm_launch_count": (C.c_uint64, []),
     "flashgmm_max_encoded_bytes": (_sz, [_i64]),
@@ -67,6 +74,15 @@ _SIGS = {
     "flashgmm_gmm_prologue_gather": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, C.c_int, _i64, _vp, _vp, _vp,
                                                _vp, _vp]),
     "flashgmm_gmm_epilogue_scatter": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _vp, _vp]),
+    "flashgmm_gmm_prologue_scan_batch": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
+    "flashgmm_gmm_prologue_gather_batch": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, C.c_int, _vp, _vp, _vp,
+                                                     _vp, _vp, _vp]),
+    "flashgmm_gmm_epilogue_scatter_batch": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp]),
+    "flashgmm_eb_compress_batch": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp,
+                                             C.POINTER(Stream), _vp]),
+    "flashgmm_eb_decompress_batch": (C.c_int, [_vp, C.POINTER(Stream), _i64, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp]),
+    "flashgmm_scalar_gaussian_encode": (C.c_int, [_vp, _vp, _i64, C.c_int, _vp, _sz, C.POINTER(_sz)]),
+    "flashgmm_scalar_gaussian_decode": (C.c_int, [_vp, _sz, _vp, _i64, C.c_int, _i32, _vp]),
     "flashgmm_rans_push_packed": (C.c_int, [_vp, _vp, _i64, _vp, _sz, C.POINTER(_sz)]),
     "flashgmm_rans_pop_table": (C.c_int, [_vp, _sz, _vp, _i64, _i64, _i32, _vp]),
     "flashgmm_rans_encode_table": (C.c_int, [_vp, _vp, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _sz, C.POINTER(_sz)]),

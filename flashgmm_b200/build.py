@@ -31,7 +31,14 @@ UNITS = [
     ("gmm_push.cu", ["-Xptxas", "-v"]),
     ("gmm_prologue.cu", []),
     ("gmm_likelihood.cu", ["-Xptxas", "-v"]),
+    ("gmm_table.cu", []),
     ("flashgmm_abi.cu", ["-Xcompiler", "-march=x86-64-v3"]),
+    ("abi_glue.cu", ["-Xcompiler", "-march=x86-64-v3"]),
+    ("abi_table.cu", ["-Xcompiler", "-march=x86-64-v3"]),
+]
+# plain C++ units built by g++ with the reference's own flags (setup.py:72-76; FMA available)
+CXX_UNITS = [
+    ("scalar_gaussian.cpp", ["-O3", "-std=c++17", "-fPIC", "-march=x86-64-v3", "-ffp-contract=fast"]),
 ]
 
 
@@ -61,6 +68,16 @@ def build(force: bool = False, verbose: bool = True) -> Path:
         objs.append(o)
         if force or _stale(o, [s, Path(__file__)] + hdrs):
             cmd = [cc, *ARCH, *COMMON, *extra, "-c", str(s), "-o", str(o)]
+            if verbose:
+                print("+", " ".join(cmd), flush=True)
+            subprocess.run(cmd, check=True)
+    cxx = os.environ.get("CXX") or shutil.which("g++") or "g++"
+    for src, flags in CXX_UNITS:
+        s = CSRC / src
+        o = objdir / (s.stem + ".o")
+        objs.append(o)
+        if force or _stale(o, [s, Path(__file__)]):
+            cmd = [cxx, *flags, "-c", str(s), "-o", str(o)]
             if verbose:
                 print("+", " ".join(cmd), flush=True)
             subprocess.run(cmd, check=True)

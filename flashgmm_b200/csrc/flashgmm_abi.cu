@@ -9,344 +9,17 @@
 //   decode: chunks in forward order: [H2D params] -> cdf-table kernel -> D2H rows;
 //           the host pops chunk c while c+1, c+2 are in flight.
 // Batch calls spread independent streams over the ctx's lanes (one worker thread each).
-#include <atomic>
-#include <chrono>
-#include <algorithm>
-#include <condition_variable>
-#include <cstdarg>
-#include <cstdio>
-#include <functional>
-#include <memory>
-#include <mutex>
-#include <string>
-#include <thread>
-#include <vector>
+#include "abi_common.hpp"
 
-#include "../../include/flashgmm.h"
-#include "gmm_kernels.h"
-#include "rans_host.hpp"
-
-using namespace flashgmm;
-
-namespace {
-
+namespace flashgmm_abi {
 thread_local std::string g_err;
 std::atomic<uint64_t> g_launches{0};
-
-// Optional per-kernel timing (bench.py's live roofline): CUDA events around each
-// launch on the launching stream, read back when the chunk is consumed.
-enum { PROF_STARTFREQ = 0, PROF_TABLE = 1, PROF_IL_ENC = 2, PROF_IL_DEC = 3, PROF_POP = 4, PROF_PUSH = 5, PROF_KINDS = 6 };
 std::atomic<int> g_prof_on{0};
 std::mutex g_prof_mu;
 double g_prof_ms[PROF_KINDS] = {};
 double g_prof_bytes[PROF_KINDS] = {};
 uint64_t g_prof_launches[PROF_KINDS] = {};
-
-int fail(int code, const char* fmt, ...) {
-    char buf[512];
-    va_list ap;
-    va_start(ap, fmt);
-    vsnprintf(buf, sizeof buf, fmt, ap);
-    va_end(ap);
-    g_err = buf;
-    return code;
-}
-
-#define CU_TRY(expr)                                                                          \
-    do {                                                                                      \
-        cudaError_t e__ = (expr);                                                             \
-        if (e__ != cudaSuccess)                                                               \
-            return fail(FLASHGMM_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), \
-                        __FILE__, __LINE__);                                                  \
-    } while (0)
-
-constexpr int kSlots = 3;
-
-long env_long(const char* name, long dflt) {
-    const char* v = getenv(name);
-    return (v && *v) ? atol(v) : dflt;
-}
-
-// Grow-only device / pinned buffers.
-struct DevBuf {
-    void* p = nullptr;
-    size_t cap = 0;
-    cudaError_t need(size_t bytes) {
-        if (bytes <= cap) return cudaSuccess;
-        if (p) cudaFree(p);
-        p = nullptr; cap = 0;
-        size_t want = bytes + bytes / 4;
-        cudaError_t e = cudaMalloc(&p, want);
-        if (e == cudaSuccess) cap = want;
-        return e;
-    }
-    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
-};
-struct PinBuf {
-    void* p = nullptr;
-    size_t cap = 0;
-    cudaError_t need(size_t bytes) {
-        if (bytes <= cap) return cudaSuccess;
-        if (p) cudaFreeHost(p);
-        p = nullptr; cap = 0;
-        size_t want = bytes + bytes / 4;
-        cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocDefault);
-        if (e == cudaSuccess) cap = want;
-        return e;
-    }
-    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
-};
-
-struct Slot {
-    cudaStream_t st = nullptr;
-    cudaEvent_t ev = nullptr;
-    cudaEvent_t k0 = nullptr, k1 = nullptr;   // kernel timing (profiling only)
-    int prof_kind = -1;
-    double prof_bytes = 0;
-    DevBuf d_in;      // staged symbols + parameters (host-memory callers)
-    DevBuf d_out;     // packed words / table rows
-    PinBuf h_out;     // D2H landing zone
-    PinBuf h_sym;     // lazily fetched symbols (device-memory callers, bypass only)
-};
-
-struct Lane {
-    Slot slot[kSlots];
-    // ONE CUDA stream per lane, shared by its slots (the slots only rotate buffers and events):
-    // the whole library then stays below the 32 hardware queues it asks for, and no worker's
-    // copy ever queues behind another stream's long kernel (see flashgmm_more_hw_queues).
-    cudaStream_t st = nullptr;
-    BackBuffer bb;
-    PinBuf h_dec;     // decoded symbols before H2D (device-memory callers)
-    bool ready = false;
-    int init() {
-        if (ready) return FLASHGMM_OK;
-        CU_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
-        for (auto& s : slot) {
-            s.st = st;
-            CU_TRY(cudaEventCreateWithFlags(&s.ev, cudaEventDisableTiming));
-            CU_TRY(cudaEventCreate(&s.k0));
-            CU_TRY(cudaEventCreate(&s.k1));
-        }
-        ready = true;
-        return FLASHGMM_OK;
-    }
-    void destroy() {
-        if (st) cudaStreamDestroy(st);
-        st = nullptr;
-        for (auto& s : slot) {
-            if (s.ev) cudaEventDestroy(s.ev);
-            if (s.k0) cudaEventDestroy(s.k0);
-            if (s.k1) cudaEventDestroy(s.k1);
-            s.d_in.release(); s.d_out.release(); s.h_out.release(); s.h_sym.release();
-            s.st = nullptr; s.ev = nullptr;
-        }
-        h_dec.release();
-        ready = false;
-    }
-};
-
-// Minimal persistent worker pool: run(fn, count) executes fn(worker_index) on
-// `count` workers and waits.
-class Pool {
-public:
-    explicit Pool(int n) : n_(n) {
-        for (int i = 0; i < n; ++i) th_.emplace_back([this, i] { loop(i); });
-    }
-    ~Pool() {
-        { std::lock_guard<std::mutex> g(m_); stop_ = true; ++gen_; }
-        cv_.notify_all();
-        for (auto& t : th_) t.join();
-    }
-    int size() const { return n_; }
-    void run(const std::function<void(int)>& fn, int count) {
-        std::unique_lock<std::mutex> g(m_);
-        fn_ = &fn; want_ = std::min(count, n_); done_ = 0; ++gen_;
-        cv_.notify_all();
-        cv_done_.wait(g, [this] { return done_ == want_; });
-        fn_ = nullptr;
-    }
-private:
-    void loop(int i) {
-        uint64_t seen = 0;
-        for (;;) {
-            const std::function<void(int)>* fn;
-            {
-                std::unique_lock<std::mutex> g(m_);
-                cv_.wait(g, [&] { return gen_ != seen; });
-                seen = gen_;
-                if (stop_) return;
-                if (i >= want_) continue;
-                fn = fn_;
-            }
-            (*fn)(i);
-            { std::lock_guard<std::mutex> g(m_); ++done_; }
-            cv_done_.notify_one();
-        }
-    }
-    int n_;
-    std::vector<std::thread> th_;
-    std::mutex m_;
-    std::condition_variable cv_, cv_done_;
-    const std::function<void(int)>* fn_ = nullptr;
-    int want_ = 0, done_ = 0;
-    uint64_t gen_ = 0;
-    bool stop_ = false;
-};
-
-// Buffers, streams and events of the device-resident decode path.
-constexpr int kRowBufs = 3;        // per group: rows run up to 2 work items ahead of the group's pop kernel
-constexpr int kPopGroups = 6;      // streams are grouped by length; every group has its own pop stream
-struct DevDecode {
-    cudaStream_t st_rows = nullptr, st_copy = nullptr, st_words = nullptr;
-    cudaStream_t st_pop[kPopGroups] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    std::vector<cudaEvent_t> ev_rows, ev_pop, ev_up;      // one per chunk (grown on demand)
-    std::vector<cudaEvent_t> t0, t1;                      // kernel timing pairs (profiling only)
-    cudaEvent_t ev_words[kPopGroups] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // a group's bitstreams are up
-    DevBuf rows[kPopGroups][kRowBufs], words, desc, state, params, out, claim;
-    int n_sm = 0;
-    PinBuf h_desc, h_words, h_state;
-    int init() {
-        if (st_rows) return FLASHGMM_OK;
-        int lo_prio = 0, hi_prio = 0;                     // the serial pop kernel is the critical path
-        CU_TRY(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
-        for (auto& sp : st_pop) CU_TRY(cudaStreamCreateWithPriority(&sp, cudaStreamNonBlocking, hi_prio));
-        CU_TRY(cudaStreamCreateWithPriority(&st_rows, cudaStreamNonBlocking, hi_prio < lo_prio ? hi_prio + 1 : lo_prio));
-        CU_TRY(cudaStreamCreateWithPriority(&st_copy, cudaStreamNonBlocking, lo_prio));
-        CU_TRY(cudaStreamCreateWithPriority(&st_words, cudaStreamNonBlocking, hi_prio));
-        for (auto& e : ev_words) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-        return FLASHGMM_OK;
-    }
-    int need_events(size_t n) {
-        while (ev_rows.size() < n) {
-            cudaEvent_t a, b, c;
-            CU_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
-            CU_TRY(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
-            CU_TRY(cudaEventCreateWithFlags(&c, cudaEventDisableTiming));
-            ev_rows.push_back(a); ev_pop.push_back(b); ev_up.push_back(c);
-        }
-        return FLASHGMM_OK;
-    }
-    int need_timers(size_t n) {
-        while (t0.size() < n) {
-            cudaEvent_t a, b;
-            CU_TRY(cudaEventCreate(&a));
-            CU_TRY(cudaEventCreate(&b));
-            t0.push_back(a); t1.push_back(b);
-        }
-        return FLASHGMM_OK;
-    }
-    void destroy() {
-        for (auto v : {&ev_rows, &ev_pop, &ev_up, &t0, &t1}) { for (auto e : *v) cudaEventDestroy(e); v->clear(); }
-        for (auto& e : ev_words) { if (e) cudaEventDestroy(e); e = nullptr; }
-        if (st_rows) cudaStreamDestroy(st_rows);
-        for (auto& sp : st_pop) { if (sp) cudaStreamDestroy(sp); sp = nullptr; }
-        if (st_copy) cudaStreamDestroy(st_copy);
-        if (st_words) cudaStreamDestroy(st_words);
-        st_rows = st_copy = st_words = nullptr;
-        for (auto& gr : rows) for (auto& r : gr) r.release();
-        words.release(); desc.release(); state.release(); claim.release();
-        params.release(); out.release(); h_desc.release(); h_words.release(); h_state.release();
-    }
-};
-
-// Buffers of the device-resident encode path (batched startfreq kernel -> push kernel).
-struct DevEncode {
-    cudaStream_t st = nullptr;
-    cudaEvent_t t[4] = {nullptr, nullptr, nullptr, nullptr};
-    cudaEvent_t ev_sf = nullptr;          // the device part's CDF pass is done (its inputs have crossed PCIe)
-    DevBuf packed, scratch, desc, rcp, result;
-    PinBuf h_desc, h_result, h_out;
-    bool rcp_ready = false;
-    // a batch in flight between encode_batch_device_begin and _finish
-    std::vector<int> act;
-    int worst = FLASHGMM_OK;
-    bool prof = false;
-    double total_n = 0;
-    int init() {
-        if (st) return FLASHGMM_OK;
-        CU_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
-        for (auto& e : t) CU_TRY(cudaEventCreate(&e));
-        CU_TRY(cudaEventCreateWithFlags(&ev_sf, cudaEventDisableTiming));
-        return FLASHGMM_OK;
-    }
-    void destroy() {
-        if (st) cudaStreamDestroy(st);
-        for (auto& e : t) if (e) { cudaEventDestroy(e); e = nullptr; }
-        if (ev_sf) { cudaEventDestroy(ev_sf); ev_sf = nullptr; }
-        st = nullptr; rcp_ready = false;
-        packed.release(); scratch.release(); desc.release(); rcp.release(); result.release();
-        h_desc.release(); h_result.release(); h_out.release();
-    }
-};
-
-// Buffers of the batched host-push path (one startfreq launch per wave of all streams, records
-// written straight into page-locked host memory, worker threads push them as the waves land).
-struct HostWaves {
-    cudaStream_t st = nullptr, st_down = nullptr;    // CDF kernels | copies of their records to the host
-    std::vector<cudaEvent_t> ev, evk, t0, t1;        // per wave: records are on the host | kernel done
-    DevBuf desc, d_packed;
-    PinBuf h_desc, h_packed;
-    // one word buffer per stream, reused across calls; each on its own cache lines (workers on
-    // neighbouring streams would otherwise fight over the line holding the write cursors)
-    struct alignas(128) PaddedBuffer { BackBuffer b; };
-    std::vector<std::unique_ptr<PaddedBuffer>> bb;
-    int init() {
-        if (st) return FLASHGMM_OK;
-        CU_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
-        CU_TRY(cudaStreamCreateWithFlags(&st_down, cudaStreamNonBlocking));
-        return FLASHGMM_OK;
-    }
-    int need_events(size_t n, bool timers) {
-        while (ev.size() < n) {
-            cudaEvent_t e, k;
-            CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-            CU_TRY(cudaEventCreateWithFlags(&k, cudaEventDisableTiming));
-            ev.push_back(e); evk.push_back(k);
-        }
-        while (timers && t0.size() < n) {
-            cudaEvent_t a, b;
-            CU_TRY(cudaEventCreate(&a));
-            CU_TRY(cudaEventCreate(&b));
-            t0.push_back(a); t1.push_back(b);
-        }
-        return FLASHGMM_OK;
-    }
-    void destroy() {
-        for (auto v : {&ev, &evk, &t0, &t1}) { for (auto e : *v) cudaEventDestroy(e); v->clear(); }
-        if (st) cudaStreamDestroy(st);
-        if (st_down) cudaStreamDestroy(st_down);
-        st = st_down = nullptr;
-        desc.release(); d_packed.release(); h_desc.release(); h_packed.release();
-        bb.clear();
-    }
-};
-
-}  // namespace
-
-struct flashgmm_ctx {
-    int device = 0;
-    std::mutex mu;
-    std::vector<std::unique_ptr<Lane>> lanes;   // lane 0 = caller's thread; 1.. = workers
-    std::unique_ptr<Pool> pool;
-    int64_t enc_chunk = 1 << 20, enc_first = 16384;
-    int64_t dec_chunk_bytes = 16 << 20, dec_first = 8192;
-    int n_workers = 8;
-    // interleaved coder (whole-stream buffers, lane 0's first stream)
-    DevBuf il_scratch, il_segw, il_out, il_err;
-    PinBuf il_host;
-    // device-resident decode (rows kernel -> pop kernel, nothing but symbols leaves the GPU)
-    std::unique_ptr<DevDecode> dd;
-    int pop_min_streams = 4;          // batches at least this large decode on the device
-    int64_t pop_rows_budget = 256ll << 20;
-    // device-resident encode (startfreq kernel -> push kernel): chosen per call by a cost model
-    std::unique_ptr<DevEncode> de;
-    std::unique_ptr<HostWaves> hw;
-    DevBuf pr_dev;                    // compress prologue: extrema codes + bitmap
-    PinBuf pr_host;
-    std::mutex de_mu;                 // the device encode path owns its buffers and stream: it runs beside the workers
-    int push_policy = 0;              // 0 auto, 1 always host workers, 2 always device
-    double push_host_ns = 4.5, push_dev_ns = 46.0;   // per symbol: one host worker / one device warp (measured, B200 box)
-};
+}  // namespace flashgmm_abi
 
 namespace {
 
@@ -1016,14 +689,11 @@ bool want_device_pop(const flashgmm_ctx* ctx, const flashgmm_stream* streams, in
 
 
 // The library keeps up to ~20 CUDA streams busy at once (one per worker thread, the device
-// encoder's, the device decoder's four). With the driver's default of 8 hardware queues streams
-// share queues, and a copy or event queued behind a long kernel stalls every stream that shares its
+// encoder's, the device decoder's). With the driver's default of 8 hardware queues streams share
+// queues, and a copy or event queued behind a long kernel stalls every stream that shares its
 // queue (measured: batch encode 6.1 ms -> 5.0 ms with 32 queues). The setting is read when the
-// CUDA context is created, so it only takes effect if this library is loaded before that; a
-// value set by the user wins.
-__attribute__((constructor)) static void flashgmm_more_hw_queues() {
-    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
-}
+// CUDA context is created, so the host must ask for it BEFORE that (flashgmm_request_hw_queues);
+// the library no longer touches the process environment on load, and works with the default.
 
 // ---------------- encode a batch of streams entirely on the device ----------------
 // batched startfreq kernel -> push kernel (one warp per stream) -> one D2H of the words.
@@ -1491,7 +1161,15 @@ int encode_batch_waves(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_stream
 // ============================ extern "C" surface ============================
 extern "C" {
 
-int flashgmm_version(void) { return 100; }
+int flashgmm_version(void) { return 200; }
+
+int flashgmm_request_hw_queues(int n) {
+    if (n < 1 || n > 32) return fail(FLASHGMM_EINVAL, "n must be in [1, 32]");
+    char buf[16];
+    snprintf(buf, sizeof buf, "%d", n);
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", buf, 0);           // a value set by the user wins
+    return FLASHGMM_OK;
+}
 
 const char* flashgmm_last_error(void) { return g_err.c_str(); }
 
@@ -1556,7 +1234,7 @@ void flashgmm_ctx_destroy(flashgmm_ctx* ctx) {
     if (ctx->dd) ctx->dd->destroy();
     if (ctx->de) ctx->de->destroy();
     if (ctx->hw) ctx->hw->destroy();
-    ctx->pr_dev.release(); ctx->pr_host.release();
+    ctx->pr_dev.release(); ctx->eb_dev.release(); ctx->eb_host.release(); ctx->pr_host.release();
     ctx->il_scratch.release(); ctx->il_segw.release(); ctx->il_out.release(); ctx->il_err.release();
     ctx->il_host.release();
     delete ctx;
@@ -1696,62 +1374,6 @@ int flashgmm_gmm_decode_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int n
     if (n_streams < 0 || (n_streams > 0 && !streams)) return fail(FLASHGMM_EINVAL, "bad stream array");
     if (want_device_pop(ctx, streams, n_streams)) return decode_batch_device(ctx, streams, n_streams, mode, mem);
     return run_batch(ctx, streams, n_streams, mode, mem, decode_stream);
-}
-
-// ---- compress / decompress glue ----
-int flashgmm_gmm_prologue_scan(flashgmm_ctx* ctx, const float* y_d, int64_t C, int64_t HW, float* yq_out_d,
-                               int64_t* bitmap_out_d, int32_t* bitmap_out_h, float* y_max_h, float* y_min_h,
-                               void* stream) {
-    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
-    if (C < 0 || HW < 0 || C > (1 << 20)) return fail(FLASHGMM_EINVAL, "bad shape C=%lld HW=%lld", (long long)C, (long long)HW);
-    if (C > 0 && HW > 0 && (!y_d || !yq_out_d)) return fail(FLASHGMM_EINVAL, "null tensor");
-    if (!bitmap_out_h || !y_max_h || !y_min_h) return fail(FLASHGMM_EINVAL, "null host output");
-    std::lock_guard<std::mutex> g(ctx->mu);
-    CU_TRY(cudaSetDevice(ctx->device));
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    CU_TRY(ctx->pr_dev.need((size_t)(C + 2) * 4));
-    CU_TRY(ctx->pr_host.need((size_t)(C + 2) * 4));
-    uint32_t* d = static_cast<uint32_t*>(ctx->pr_dev.p);          // [0..1] extrema codes, [2..] bitmap32
-    CU_TRY(launch_gmm_prologue_scan(y_d, (int)C, HW, yq_out_d, reinterpret_cast<long long*>(bitmap_out_d),
-                                    reinterpret_cast<int32_t*>(d + 2), d, st));
-    g_launches.fetch_add(1, std::memory_order_relaxed);
-    CU_TRY(cudaMemcpyAsync(ctx->pr_host.p, d, (size_t)(C + 2) * 4, cudaMemcpyDeviceToHost, st));
-    CU_TRY(cudaStreamSynchronize(st));
-    const uint32_t* h = static_cast<const uint32_t*>(ctx->pr_host.p);
-    const bool empty = C == 0 || HW == 0;
-    *y_max_h = empty ? 0.0f : gmm_extremum_from_bits(h[0]);
-    *y_min_h = empty ? 0.0f : gmm_extremum_from_bits(h[1]);
-    memcpy(bitmap_out_h, h + 2, (size_t)C * 4);
-    return FLASHGMM_OK;
-}
-
-int flashgmm_gmm_prologue_gather(flashgmm_ctx* ctx, const float* yq_d, const float* scales_d, const float* means_d,
-                                 const float* weights_d, const int64_t* bitmap_d, int64_t C, int64_t HW, int K,
-                                 int64_t n_sym, int32_t* symbols_out_d, float* scales_out_d, float* means_out_d,
-                                 float* weights_out_d, void* stream) {
-    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
-    if (C < 0 || HW < 0 || n_sym < 0 || K < 1 || K > 8 || C > (1 << 20) || (HW > 0 && n_sym % HW != 0))
-        return fail(FLASHGMM_EINVAL, "bad shape C=%lld HW=%lld K=%d n_sym=%lld", (long long)C, (long long)HW, K, (long long)n_sym);
-    if (n_sym > 0 && (!scales_d || !means_d || !weights_d || !bitmap_d || !scales_out_d || !means_out_d || !weights_out_d))
-        return fail(FLASHGMM_EINVAL, "null tensor");
-    CU_TRY(cudaSetDevice(ctx->device));
-    CU_TRY(launch_gmm_prologue_gather(yq_d, scales_d, means_d, weights_d, reinterpret_cast<const long long*>(bitmap_d),
-                                      (int)C, HW, K, n_sym, symbols_out_d, scales_out_d, means_out_d, weights_out_d,
-                                      static_cast<cudaStream_t>(stream)));
-    g_launches.fetch_add(1, std::memory_order_relaxed);
-    return FLASHGMM_OK;
-}
-
-int flashgmm_gmm_epilogue_scatter(flashgmm_ctx* ctx, const int32_t* symbols_d, const int64_t* bitmap_d, int64_t C,
-                                  int64_t HW, float* y_hat_out_d, void* stream) {
-    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
-    if (C < 0 || HW < 0 || C > (1 << 20)) return fail(FLASHGMM_EINVAL, "bad shape C=%lld HW=%lld", (long long)C, (long long)HW);
-    if (C > 0 && HW > 0 && (!bitmap_d || !y_hat_out_d)) return fail(FLASHGMM_EINVAL, "null tensor");
-    CU_TRY(cudaSetDevice(ctx->device));
-    CU_TRY(launch_gmm_epilogue_scatter(symbols_d, reinterpret_cast<const long long*>(bitmap_d), (int)C, HW, y_hat_out_d,
-                                       static_cast<cudaStream_t>(stream)));
-    g_launches.fetch_add(1, std::memory_order_relaxed);
-    return FLASHGMM_OK;
 }
 
 // ---- interleaved multi-lane rANS ----
@@ -1948,226 +1570,6 @@ int flashgmm_gmm_likelihood_bwd(flashgmm_ctx* ctx, const float* y_d, const float
                                      grad_y_d, grad_scales_d, grad_means_d, grad_weights_d, st));
     g_launches.fetch_add(1, std::memory_order_relaxed);
     if (!stream) CU_TRY(cudaStreamSynchronize(st));
-    return FLASHGMM_OK;
-}
-
-// ---- host-only halves ----
-static int emit(BackBuffer& bb, uint8_t* out, size_t cap, size_t* out_len) {
-    *out_len = bb.bytes();
-    if (*out_len > cap) return fail(FLASHGMM_ENOSPC, "output buffer too small: need %zu bytes, have %zu", *out_len, cap);
-    memcpy(out, bb.data(), *out_len);
-    return FLASHGMM_OK;
-}
-
-int flashgmm_rans_push_packed(const uint32_t* packed, const int32_t* symbols, int64_t n, uint8_t* out,
-                              size_t out_cap, size_t* out_len) {
-    if (!out_len || (n > 0 && !packed) || n < 0 || (!out && out_cap)) return fail(FLASHGMM_EINVAL, "bad argument");
-    if (!symbols)
-        for (int64_t i = 0; i < n; ++i)
-            if ((packed[i] >> 16) == 0) return fail(FLASHGMM_EINVAL, "bypass record at %lld needs symbols", (long long)i);
-    BackBuffer bb((size_t)(n * 9 / 16) + 64);
-    RansEncoder64 enc;
-    enc.init(&bb);
-    enc.push_chunk_reverse(packed, symbols, n);
-    enc.flush();
-    return emit(bb, out, out_cap, out_len);
-}
-
-int flashgmm_rans_pop_table(const uint8_t* encoded, size_t encoded_len, const uint16_t* table,
-                            int64_t row_stride, int64_t n, int32_t R, int32_t* symbols_out) {
-    if (!encoded || n < 0 || (n > 0 && (!table || !symbols_out)) || R < 0 || row_stride != table_row_stride(R))
-        return fail(FLASHGMM_EINVAL, "bad argument");
-    RansDecoder64 dec;
-    dec.init(encoded, encoded_len);
-    pop_rows(dec, table, row_stride, R, n, symbols_out);
-    if (dec.overrun) return fail(FLASHGMM_ETRUNC, "bitstream truncated");
-    return FLASHGMM_OK;
-}
-
-static int check_table_args(const int32_t* indexes, int64_t n, const int32_t* cdfs, int64_t n_cdfs,
-                            int64_t cdf_stride, const int32_t* sizes, const int32_t* offsets) {
-    if (n < 0 || n_cdfs < 0 || (n > 0 && (!indexes || !cdfs || !sizes || !offsets)))
-        return fail(FLASHGMM_EINVAL, "bad argument");
-    for (int64_t c = 0; c < n_cdfs; ++c)
-        if (sizes[c] < 2 || sizes[c] > cdf_stride) return fail(FLASHGMM_EINVAL, "cdf_sizes[%lld]=%d invalid", (long long)c, sizes[c]);
-    for (int64_t i = 0; i < n; ++i)
-        if (indexes[i] < 0 || indexes[i] >= n_cdfs) return fail(FLASHGMM_EINVAL, "indexes[%lld]=%d out of range", (long long)i, indexes[i]);
-    return FLASHGMM_OK;
-}
-
-int flashgmm_rans_encode_table(const int32_t* symbols, const int32_t* indexes, int64_t n,
-                               const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
-                               const int32_t* cdf_sizes, const int32_t* offsets, uint8_t* out,
-                               size_t out_cap, size_t* out_len) {
-    if (!out_len || (n > 0 && !symbols)) return fail(FLASHGMM_EINVAL, "bad argument");
-    int rc = check_table_args(indexes, n, cdfs, n_cdfs, cdf_stride, cdf_sizes, offsets);
-    if (rc) return rc;
-    BackBuffer bb((size_t)(n * 9 / 16) + 64);
-    RansEncoder64 enc;
-    enc.init(&bb);
-    for (int64_t i = n - 1; i >= 0; --i) {             // reverse walk of rans_interface.cpp:343-398
-        bb.reserve(24);
-        const int32_t ci = indexes[i];
-        const int32_t* cdf = cdfs + (int64_t)ci * cdf_stride;
-        const int32_t max_value = cdf_sizes[ci] - 2;
-        int32_t value = symbols[i] - offsets[ci];
-        uint32_t raw = 0;
-        if (value < 0) { raw = (uint32_t)(-2 * value - 1); value = max_value; }
-        else if (value >= max_value) { raw = (uint32_t)(2 * (value - max_value)); value = max_value; }
-        if (value == max_value) {
-            int nb = 0;
-            while (nb < 8 && (raw >> (nb * 4)) != 0) ++nb;
-            for (int j = nb - 1; j >= 0; --j) enc.put_bits4((raw >> (4 * j)) & kBypassMax);
-            enc.put_bits4((uint32_t)nb);
-        }
-        const uint32_t start = (uint32_t)cdf[value] & 0xffffu;
-        const uint32_t freq = (uint32_t)(cdf[value + 1] - cdf[value]) & 0xffffu;
-        if (freq == 0) return fail(FLASHGMM_EINVAL, "zero-frequency symbol at %lld (invalid CDF)", (long long)i);
-        enc.put(start, freq);
-    }
-    enc.flush();
-    return emit(bb, out, out_cap, out_len);
-}
-
-static void decode_table_run(RansDecoder64& dec, const int32_t* indexes, int64_t n, const int32_t* cdfs,
-                             int64_t cdf_stride, const int32_t* cdf_sizes, const int32_t* offsets,
-                             int32_t* symbols_out) {
-    for (int64_t i = 0; i < n; ++i) {
-        const int32_t ci = indexes[i];
-        const int32_t* cdf = cdfs + (int64_t)ci * cdf_stride;
-        const int32_t sz = cdf_sizes[ci], max_value = sz - 2;
-        const uint32_t cum = dec.get();
-        const int32_t* it = std::lower_bound(cdf, cdf + sz, (int32_t)(cum + 1));
-        int32_t sidx = (int32_t)(it - cdf) - 1;
-        if (sidx < 0) sidx = 0;
-        if (sidx > max_value) sidx = max_value;
-        dec.advance((uint32_t)cdf[sidx], (uint32_t)(cdf[sidx + 1] - cdf[sidx]));
-        int32_t value = sidx;
-        if (value == max_value) {
-            int32_t vb = (int32_t)dec.get_bits4(), nb = vb;
-            while (vb == (int32_t)kBypassMax && !dec.overrun) { vb = (int32_t)dec.get_bits4(); nb += vb; }
-            int32_t raw = 0;
-            for (int32_t j = 0; j < nb && !dec.overrun; ++j) raw |= (int32_t)(dec.get_bits4() << ((j * 4) & 31));
-            value = raw >> 1;
-            if (raw & 1) value = -value - 1; else value += max_value;
-        }
-        symbols_out[i] = value + offsets[ci];
-    }
-}
-
-int flashgmm_rans_decode_table(const uint8_t* encoded, size_t encoded_len, const int32_t* indexes,
-                               int64_t n, const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
-                               const int32_t* cdf_sizes, const int32_t* offsets, int32_t* symbols_out) {
-    if (!encoded || (n > 0 && !symbols_out)) return fail(FLASHGMM_EINVAL, "bad argument");
-    int rc = check_table_args(indexes, n, cdfs, n_cdfs, cdf_stride, cdf_sizes, offsets);
-    if (rc) return rc;
-    RansDecoder64 dec;
-    dec.init(encoded, encoded_len);
-    decode_table_run(dec, indexes, n, cdfs, cdf_stride, cdf_sizes, offsets, symbols_out);
-    if (dec.overrun) return fail(FLASHGMM_ETRUNC, "bitstream truncated");
-    return FLASHGMM_OK;
-}
-
-// ---- sessions ----
-struct flashgmm_buffered_encoder {
-    struct Sym { uint16_t start, range; uint8_t bypass; };     // rans_interface.hpp:48-52
-    std::vector<Sym> syms;
-    inline void raw_nibbles(uint32_t raw) {                     // count prefix + nibbles, RI:372-397 / 524-552
-        int32_t nb = 0;
-        while (nb < 8 && (raw >> (nb * 4)) != 0) ++nb;
-        int32_t v = nb;
-        while (v >= (int32_t)kBypassMax) { syms.push_back({(uint16_t)kBypassMax, (uint16_t)(kBypassMax + 1), 1}); v -= kBypassMax; }
-        syms.push_back({(uint16_t)v, (uint16_t)(v + 1), 1});
-        for (int32_t j = 0; j < nb; ++j) {
-            uint16_t q = (uint16_t)((raw >> (j * 4)) & kBypassMax);
-            syms.push_back({q, (uint16_t)(q + 1), 1});
-        }
-    }
-};
-
-int flashgmm_benc_create(flashgmm_buffered_encoder** out) {
-    if (!out) return fail(FLASHGMM_EINVAL, "null out pointer");
-    *out = new flashgmm_buffered_encoder();
-    rcp_table();
-    return FLASHGMM_OK;
-}
-void flashgmm_benc_destroy(flashgmm_buffered_encoder* enc) { delete enc; }
-int64_t flashgmm_benc_entries(const flashgmm_buffered_encoder* enc) { return enc ? (int64_t)enc->syms.size() : -1; }
-
-int flashgmm_benc_push_table(flashgmm_buffered_encoder* enc, const int32_t* symbols, const int32_t* indexes,
-                             int64_t n, const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
-                             const int32_t* cdf_sizes, const int32_t* offsets) {
-    if (!enc || (n > 0 && !symbols)) return fail(FLASHGMM_EINVAL, "bad argument");
-    int rc = check_table_args(indexes, n, cdfs, n_cdfs, cdf_stride, cdf_sizes, offsets);
-    if (rc) return rc;
-    for (int64_t i = 0; i < n; ++i) {
-        const int32_t ci = indexes[i];
-        const int32_t* cdf = cdfs + (int64_t)ci * cdf_stride;
-        const int32_t max_value = cdf_sizes[ci] - 2;
-        int32_t value = symbols[i] - offsets[ci];
-        uint32_t raw = 0;
-        if (value < 0) { raw = (uint32_t)(-2 * value - 1); value = max_value; }
-        else if (value >= max_value) { raw = (uint32_t)(2 * (value - max_value)); value = max_value; }
-        const uint16_t range = (uint16_t)(cdf[value + 1] - cdf[value]);
-        if (range == 0) return fail(FLASHGMM_EINVAL, "zero-frequency symbol at %lld (invalid CDF)", (long long)i);
-        enc->syms.push_back({(uint16_t)cdf[value], range, 0});
-        if (value == max_value) enc->raw_nibbles(raw);
-    }
-    return FLASHGMM_OK;
-}
-
-int flashgmm_benc_push_gmm_packed(flashgmm_buffered_encoder* enc, const uint32_t* packed,
-                                  const int32_t* symbols, int64_t n) {
-    if (!enc || n < 0 || (n > 0 && !packed)) return fail(FLASHGMM_EINVAL, "bad argument");
-    for (int64_t i = 0; i < n; ++i) {
-        const uint32_t pk = packed[i], freq = pk >> 16;
-        if (freq) { enc->syms.push_back({(uint16_t)(pk & 0xffffu), (uint16_t)freq, 0}); continue; }
-        if (!symbols) return fail(FLASHGMM_EINVAL, "bypass record at %lld needs symbols", (long long)i);
-        enc->syms.push_back({(uint16_t)kMaxCdf, 1, 0});        // RI:513-521
-        enc->raw_nibbles((uint32_t)symbols[i]);
-    }
-    return FLASHGMM_OK;
-}
-
-int flashgmm_benc_flush(flashgmm_buffered_encoder* enc, uint8_t* out, size_t out_cap, size_t* out_len) {
-    if (!enc || !out_len || (!out && out_cap)) return fail(FLASHGMM_EINVAL, "bad argument");
-    BackBuffer bb(enc->syms.size() / 2 + 64);
-    RansEncoder64 r;
-    r.init(&bb);
-    for (size_t k = enc->syms.size(); k-- > 0;) {              // reverse walk, RI:569-577
-        if ((k & 1023) == 1023 || k + 1 == enc->syms.size()) bb.reserve(1024 + 8);
-        const auto& s = enc->syms[k];
-        if (s.bypass) r.put_bits4(s.start); else r.put(s.start, s.range);
-    }
-    r.flush();
-    int rc = emit(bb, out, out_cap, out_len);
-    if (rc == FLASHGMM_OK) enc->syms.clear();                  // on ENOSPC the caller retries with a larger buffer
-    return rc;
-}
-
-struct flashgmm_stream_decoder {
-    std::vector<uint8_t> stream;
-    RansDecoder64 dec;
-};
-
-int flashgmm_sdec_create(const uint8_t* encoded, size_t encoded_len, flashgmm_stream_decoder** out) {
-    if (!out || !encoded) return fail(FLASHGMM_EINVAL, "bad argument");
-    auto* d = new flashgmm_stream_decoder();
-    d->stream.assign(encoded, encoded + encoded_len);          // set_stream copies, RI:887
-    d->dec.init(d->stream.data(), d->stream.size());
-    *out = d;
-    return FLASHGMM_OK;
-}
-void flashgmm_sdec_destroy(flashgmm_stream_decoder* dec) { delete dec; }
-
-int flashgmm_sdec_decode_table(flashgmm_stream_decoder* dec, const int32_t* indexes, int64_t n,
-                               const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
-                               const int32_t* cdf_sizes, const int32_t* offsets, int32_t* symbols_out) {
-    if (!dec || (n > 0 && !symbols_out)) return fail(FLASHGMM_EINVAL, "bad argument");
-    int rc = check_table_args(indexes, n, cdfs, n_cdfs, cdf_stride, cdf_sizes, offsets);
-    if (rc) return rc;
-    decode_table_run(dec->dec, indexes, n, cdfs, cdf_stride, cdf_sizes, offsets, symbols_out);
-    if (dec->dec.overrun) return fail(FLASHGMM_ETRUNC, "bitstream truncated");
     return FLASHGMM_OK;
 }
 

@@ -125,15 +125,30 @@ cudaError_t launch_gmm_likelihood_bwd(const float* y, const float* sc, const flo
                                       float lik_bound, float* gy, float* gsc, float* gmu, float* gw,
                                       cudaStream_t st);
 
-// ---- compress / decompress glue (gmm_prologue.cu) ----
-cudaError_t launch_gmm_prologue_scan(const float* y, int C, int64_t HW, float* yq, long long* bitmap64,
+// ---- compress / decompress glue (gmm_prologue.cu), batches of images ----
+// One launch covers up to kPrologueMaxBatch images (the per-image output offsets travel as a kernel
+// argument). Image b: y / y_quantized / y_hat at b*C*HW, parameters at b*K*C*HW, bitmap at b*C;
+// its kept symbols at symbol offset off[b] of the outputs, its K-major block [K][n[b]] at K*off[b].
+constexpr int kPrologueMaxBatch = 64;
+struct PrologueBatch { int64_t off[kPrologueMaxBatch]; int64_t n[kPrologueMaxBatch]; };
+// extrema: 2 words per image (order-preserving codes of max and min of the unrounded y)
+cudaError_t launch_gmm_prologue_scan(const float* y, int B, int C, int64_t HW, float* yq, long long* bitmap64,
                                      int32_t* bitmap32, uint32_t* extrema, cudaStream_t st);
 cudaError_t launch_gmm_prologue_gather(const float* yq, const float* scales, const float* means, const float* weights,
-                                       const long long* bitmap, int C, int64_t HW, int K, int64_t n_sym,
+                                       const long long* bitmap, int B, int C, int64_t HW, int K, const PrologueBatch& meta,
                                        int32_t* sym_out, float* scales_out, float* means_out, float* weights_out,
                                        cudaStream_t st);
-cudaError_t launch_gmm_epilogue_scatter(const int32_t* symbols, const long long* bitmap, int C, int64_t HW,
-                                        float* y_hat, cudaStream_t st);
+cudaError_t launch_gmm_epilogue_scatter(const int32_t* symbols, const long long* bitmap, int B, int C, int64_t HW,
+                                        const PrologueBatch& meta, float* y_hat, cudaStream_t st);
 float gmm_extremum_from_bits(uint32_t code);      // inverse of the order-preserving code the scan kernel reduces with
+
+
+// ---- hyper-latent (z) branch: factorised-prior table coder records (gmm_table.cu) ----
+// rec[i] (i over (B, C, HW)): bits 0-15 start, 16-31 freq, 32-62 raw bypass value, bit 63 = the symbol took the
+// table's sentinel slot and carries a bypass payload. symbols_out (optional) receives round(z - median).
+// *err is set to 1 if a bypass value does not fit 31 bits.
+cudaError_t launch_eb_records(const float* z, const float* medians, const int32_t* cdfs, const int32_t* sizes,
+                              const int32_t* offsets, int64_t n_img, int C, int64_t HW, int cdf_stride,
+                              unsigned long long* rec, int32_t* symbols_out, uint32_t* err, cudaStream_t st);
 
 }  // namespace flashgmm

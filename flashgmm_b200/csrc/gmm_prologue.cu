@@ -30,7 +30,7 @@ __device__ __forceinline__ uint32_t ordered_bits(float f) {
 }
 
 __global__ void __launch_bounds__(kPrThreads)
-gmm_prologue_scan_kernel(const float* __restrict__ y, int64_t HW, float* __restrict__ yq,
+gmm_prologue_scan_kernel(const float* __restrict__ y, int C, int64_t HW, float* __restrict__ yq,
                          long long* __restrict__ bitmap64, int32_t* __restrict__ bitmap32,
                          uint32_t* __restrict__ extrema) {
     __shared__ float s_mx[kPrThreads / 32], s_mn[kPrThreads / 32];
@@ -60,8 +60,9 @@ gmm_prologue_scan_kernel(const float* __restrict__ y, int64_t HW, float* __restr
         if (bitmap64) bitmap64[blockIdx.x] = any;
         bitmap32[blockIdx.x] = any;
         if (HW > 0) {
-            atomicMax(extrema + 0, ordered_bits(mx));
-            atomicMin(extrema + 1, ordered_bits(mn));
+            const int b = (int)blockIdx.x / C;                 // image of this channel: extrema are per image
+            atomicMax(extrema + 2 * b, ordered_bits(mx));
+            atomicMin(extrema + 2 * b + 1, ordered_bits(mn));
         }
     }
 }
@@ -79,15 +80,24 @@ __device__ __forceinline__ int kept_before(const long long* __restrict__ bitmap,
     return tot;
 }
 
-// grid (C, 3K + 1): plane p < K scales (clamped), < 2K means, < 3K weights, == 3K symbols
+// grid (C, 3K + 1, images): plane p < K scales (clamped), < 2K means, < 3K weights, == 3K symbols.
+// Image b's kept symbols start at symbol offset meta.off[b] of the outputs and its K-major block
+// [K][meta.n[b]] at K * meta.off[b] of each parameter output.
 __global__ void __launch_bounds__(kPrThreads)
 gmm_prologue_gather_kernel(const float* __restrict__ yq, const float* __restrict__ scales,
                            const float* __restrict__ means, const float* __restrict__ weights,
-                           const long long* __restrict__ bitmap, int C, int64_t HW, int K, int64_t n_sym,
+                           const long long* __restrict__ bitmap, int C, int64_t HW, int K, PrologueBatch meta,
                            int32_t* __restrict__ sym_out, float* __restrict__ scales_out,
                            float* __restrict__ means_out, float* __restrict__ weights_out) {
     __shared__ int s_part[kPrThreads / 32];
-    const int c = blockIdx.x, p = blockIdx.y;
+    const int c = blockIdx.x, p = blockIdx.y, b = blockIdx.z;
+    const int64_t n_sym = meta.n[b], off = meta.off[b];
+    if (n_sym <= 0) return;
+    bitmap += (int64_t)b * C;
+    if (yq) yq += (int64_t)b * C * HW;
+    scales += (int64_t)b * K * C * HW; means += (int64_t)b * K * C * HW; weights += (int64_t)b * K * C * HW;
+    if (sym_out) sym_out += off;
+    scales_out += (int64_t)K * off; means_out += (int64_t)K * off; weights_out += (int64_t)K * off;
     if (bitmap[c] == 0) return;
     if (p == 3 * K && (yq == nullptr || sym_out == nullptr)) return;
     const int64_t j = kept_before(bitmap, c, s_part);
@@ -112,10 +122,12 @@ gmm_prologue_gather_kernel(const float* __restrict__ yq, const float* __restrict
 
 __global__ void __launch_bounds__(kPrThreads)
 gmm_epilogue_scatter_kernel(const int32_t* __restrict__ symbols, const long long* __restrict__ bitmap,
-                            int64_t HW, float* __restrict__ y_hat) {
+                            int C, int64_t HW, PrologueBatch meta, float* __restrict__ y_hat) {
     __shared__ int s_part[kPrThreads / 32];
-    const int c = blockIdx.x;
-    float* dst = y_hat + (int64_t)c * HW;
+    const int c = blockIdx.x, b = blockIdx.y;
+    bitmap += (int64_t)b * C;
+    if (symbols) symbols += meta.off[b];
+    float* dst = y_hat + ((int64_t)b * C + c) * HW;
     if (bitmap[c] == 0) {
         for (int64_t i = threadIdx.x; i < HW; i += kPrThreads) dst[i] = 0.0f;
         return;
@@ -127,32 +139,33 @@ gmm_epilogue_scatter_kernel(const int32_t* __restrict__ symbols, const long long
 
 }  // namespace
 
-cudaError_t launch_gmm_prologue_scan(const float* y, int C, int64_t HW, float* yq, long long* bitmap64,
+cudaError_t launch_gmm_prologue_scan(const float* y, int B, int C, int64_t HW, float* yq, long long* bitmap64,
                                      int32_t* bitmap32, uint32_t* extrema, cudaStream_t st) {
-    // extrema[0] collects the max (starts at the smallest code), extrema[1] the min (starts at the largest)
-    cudaError_t e = cudaMemsetAsync(extrema, 0x00, 4, st);
+    // per image: extrema[2b] collects the max (starts at the smallest code), extrema[2b+1] the min (the largest)
+    if (B <= 0) return cudaSuccess;
+    cudaError_t e = cudaMemset2DAsync(extrema, 8, 0x00, 4, (size_t)B, st);
     if (e != cudaSuccess) return e;
-    e = cudaMemsetAsync(extrema + 1, 0xff, 4, st);
+    e = cudaMemset2DAsync(extrema + 1, 8, 0xff, 4, (size_t)B, st);
     if (e != cudaSuccess) return e;
     if (C <= 0) return cudaSuccess;
-    gmm_prologue_scan_kernel<<<C, kPrThreads, 0, st>>>(y, HW, yq, bitmap64, bitmap32, extrema);
+    gmm_prologue_scan_kernel<<<(unsigned)(B * C), kPrThreads, 0, st>>>(y, C, HW, yq, bitmap64, bitmap32, extrema);
     return cudaGetLastError();
 }
 
 cudaError_t launch_gmm_prologue_gather(const float* yq, const float* scales, const float* means, const float* weights,
-                                       const long long* bitmap, int C, int64_t HW, int K, int64_t n_sym,
+                                       const long long* bitmap, int B, int C, int64_t HW, int K, const PrologueBatch& meta,
                                        int32_t* sym_out, float* scales_out, float* means_out, float* weights_out,
                                        cudaStream_t st) {
-    if (C <= 0 || HW <= 0 || n_sym <= 0) return cudaSuccess;
-    gmm_prologue_gather_kernel<<<dim3((unsigned)C, (unsigned)(3 * K + 1)), kPrThreads, 0, st>>>(
-        yq, scales, means, weights, bitmap, C, HW, K, n_sym, sym_out, scales_out, means_out, weights_out);
+    if (B <= 0 || C <= 0 || HW <= 0) return cudaSuccess;
+    gmm_prologue_gather_kernel<<<dim3((unsigned)C, (unsigned)(3 * K + 1), (unsigned)B), kPrThreads, 0, st>>>(
+        yq, scales, means, weights, bitmap, C, HW, K, meta, sym_out, scales_out, means_out, weights_out);
     return cudaGetLastError();
 }
 
-cudaError_t launch_gmm_epilogue_scatter(const int32_t* symbols, const long long* bitmap, int C, int64_t HW,
-                                        float* y_hat, cudaStream_t st) {
-    if (C <= 0 || HW <= 0) return cudaSuccess;
-    gmm_epilogue_scatter_kernel<<<C, kPrThreads, 0, st>>>(symbols, bitmap, HW, y_hat);
+cudaError_t launch_gmm_epilogue_scatter(const int32_t* symbols, const long long* bitmap, int B, int C, int64_t HW,
+                                        const PrologueBatch& meta, float* y_hat, cudaStream_t st) {
+    if (B <= 0 || C <= 0 || HW <= 0) return cudaSuccess;
+    gmm_epilogue_scatter_kernel<<<dim3((unsigned)C, (unsigned)B), kPrThreads, 0, st>>>(symbols, bitmap, C, HW, meta, y_hat);
     return cudaGetLastError();
 }
 

@@ -54,6 +54,11 @@ enum { FLASHGMM_MEM_HOST = 0, FLASHGMM_MEM_DEVICE = 1 };
 int flashgmm_version(void);
 const char* flashgmm_last_error(void);
 
+/* Optional, before the process creates its CUDA context: ask the driver for n hardware queues
+ * (CUDA_DEVICE_MAX_CONNECTIONS, unless the user has set it). The library keeps ~20 CUDA streams busy;
+ * with the default 8 queues it is correct but copies can queue behind long kernels. */
+int flashgmm_request_hw_queues(int n);
+
 /* Context = device + streams + staging buffers + host worker threads. */
 int flashgmm_ctx_create(int device, flashgmm_ctx** out);
 void flashgmm_ctx_destroy(flashgmm_ctx* ctx);
@@ -206,6 +211,41 @@ int flashgmm_gmm_prologue_gather(flashgmm_ctx* ctx, const float* y_quantized_d, 
 int flashgmm_gmm_epilogue_scatter(flashgmm_ctx* ctx, const int32_t* symbols_d, const int64_t* bitmap_d,
                                   int64_t C, int64_t HW, float* y_hat_out_d, void* stream);
 
+/* Batch forms: B images of one pass in ONE launch each. y / y_quantized / y_hat are (B, C, H, W) contiguous,
+ * parameters (B, K*C, H, W), bitmaps (B, C). Per-image outputs are concatenated: image b's kept symbols
+ * start at symbol offset off_b = n_sym_h[0] + ... + n_sym_h[b-1] of symbols_out_d, and its K-major block
+ * [K][n_sym_h[b]] starts at element K * off_b of each parameter output (so the coder's view of image b is
+ * base + K*off_b, stride_n = 1, stride_k = n_sym_h[b]). extrema_out_h receives 2 floats per image
+ * (max, min of the unrounded y); bitmap_out_h B*C int32. */
+int flashgmm_gmm_prologue_scan_batch(flashgmm_ctx* ctx, const float* y_d, int64_t B, int64_t C, int64_t HW,
+                                     float* y_quantized_out_d, int64_t* bitmap_out_d, int32_t* bitmap_out_h,
+                                     float* extrema_out_h, void* stream);
+int flashgmm_gmm_prologue_gather_batch(flashgmm_ctx* ctx, const float* y_quantized_d, const float* scales_d,
+                                       const float* means_d, const float* weights_d, const int64_t* bitmap_d,
+                                       int64_t B, int64_t C, int64_t HW, int K, const int64_t* n_sym_h,
+                                       int32_t* symbols_out_d, float* scales_out_d, float* means_out_d,
+                                       float* weights_out_d, void* stream);
+int flashgmm_gmm_epilogue_scatter_batch(flashgmm_ctx* ctx, const int32_t* symbols_d, const int64_t* bitmap_d,
+                                        const int64_t* n_sym_h, int64_t B, int64_t C, int64_t HW,
+                                        float* y_hat_out_d, void* stream);
+
+/* ---- hyper-latent z branch: EntropyBottleneck.compress / decompress for B images, z on the device ----
+ * EM:605-618 -> EntropyModel.compress / decompress EM:237-327 -> the table coder RI:334-399, 619-688,
+ * without the five .tolist() marshals per image: the CDF lookup runs in a kernel (gmm_table.cu), the
+ * serial push / pop on the ctx's worker threads (one image each). Element (b, c, i) uses CDF row c
+ * (EntropyBottleneck._build_indexes, EM:556-567). Byte-identical streams.
+ *   compress:   z_d (B, C, HW) float32, medians_d (C), cdfs_d (C, cdf_stride) int32, cdf_sizes_d / offsets_d (C):
+ *               device. streams[b].bytes / bytes_cap: host output buffer; bytes_len / status: out.
+ *               symbols_out_d (optional, device int32 (B, C, HW)) receives round(z - median).
+ *   decompress: streams[b].bytes / bytes_cap: the stream; cdfs / sizes / offsets: HOST copies;
+ *               symbols_out_d (device int32 (B, C, HW)); the caller adds the medians (EM:185-194). */
+int flashgmm_eb_compress_batch(flashgmm_ctx* ctx, const float* z_d, const float* medians_d, const int32_t* cdfs_d,
+                               const int32_t* cdf_sizes_d, const int32_t* offsets_d, int64_t B, int64_t C, int64_t HW,
+                               int64_t cdf_stride, int32_t* symbols_out_d, flashgmm_stream* streams, void* stream);
+int flashgmm_eb_decompress_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, int64_t B, const int32_t* cdfs_h,
+                                 const int32_t* cdf_sizes_h, const int32_t* offsets_h, int64_t C, int64_t HW,
+                                 int64_t cdf_stride, int32_t* symbols_out_d, void* stream);
+
 /* ---- host-only halves (no GPU): the serial rANS recurrence ---- */
 
 /* Push packed (start|freq<<16, freq==0 = bypass -> needs symbols[i]) records:
@@ -229,6 +269,17 @@ int flashgmm_rans_encode_table(const int32_t* symbols, const int32_t* indexes, i
 int flashgmm_rans_decode_table(const uint8_t* encoded, size_t encoded_len, const int32_t* indexes,
                                int64_t n, const int32_t* cdfs, int64_t n_cdfs, int64_t cdf_stride,
                                const int32_t* cdf_sizes, const int32_t* offsets, int32_t* symbols_out);
+
+/* Scalar single-Gaussian search coder, host only (the reference's is scalar libm code on the CPU and no
+ * shipped model calls it): RansEncoder.encode_with_indexes(symbols, scales, max_value) RI:401-456, 600-607 and
+ * RansDecoder.decode_with_indexes(encoded, scales, max_bs_value) RI:690-764, zero-mean Gaussian of scale
+ * scales[i] per symbol through the SCALAR approximations RI:148-150, 188-204, 216-219 (libm expf / sqrtf).
+ * Parity is unpinned across hosts (depends on the host's libm); byte-identical to the reference built on
+ * the same machine. */
+int flashgmm_scalar_gaussian_encode(const int32_t* symbols, const float* scales, int64_t n, int mode,
+                                    uint8_t* out, size_t out_cap, size_t* out_len);
+int flashgmm_scalar_gaussian_decode(const uint8_t* encoded, size_t encoded_len, const float* scales, int64_t n,
+                                    int mode, int32_t max_bs_value, int32_t* symbols_out);
 
 /* ---- buffered encoder / streaming decoder sessions (host state objects) ----
  * BufferedRansEncoder (RI:334-399, 458-585, 977-984): symbols of several calls accumulate

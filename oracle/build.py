@@ -98,6 +98,13 @@ def build_ref(force: bool = False):
         cmd += [src, "-o", out, f"-L{torch_lib}", f"-Wl,-rpath,{torch_lib}",
                 "-ltorch", "-ltorch_cpu", "-lc10", "-ltorch_python"]
         _run(cmd)
+    # compressai._CXX (pmf_to_quantized_cdf, used by EntropyBottleneck.update): pybind11 only, setup.py:86-97
+    ops_src = REF_ROOT / "compressai/cpp_exts/ops/ops.cpp"
+    ops_out = REF_OUT / "_CXX.so"
+    if ops_src.exists() and (force or not _newer(ops_out, ops_src)):
+        _run(["g++", "-std=c++17", "-O3", "-fPIC", "-shared", "-w", "-I", sysconfig.get_paths()["include"],
+              "-I", pybind11.get_include(), ops_src, "-o", ops_out])
+    outs.append(ops_out)
     meta = {
         "compiler": subprocess.run(["g++", "--version"], capture_output=True, text=True).stdout.splitlines()[0],
         "flags": "-std=c++17 -march={native|x86-64-v3} -O3 (setup.py:72-76)",

@@ -33,6 +33,59 @@ def _pkg(name: str, path: Path):
     return m
 
 
+def _load_cxx():
+    """The reference's ``compressai._CXX`` (oracle/_ref/_CXX.so, built by oracle/build.py) or a stub."""
+    so = Path(__file__).resolve().parent / "_ref" / "_CXX.so"
+    if so.exists():
+        import importlib.machinery
+        import importlib.util
+
+        loader = importlib.machinery.ExtensionFileLoader("_CXX", str(so))
+        spec = importlib.util.spec_from_loader("_CXX", loader)
+        mod = importlib.util.module_from_spec(spec)
+        loader.exec_module(mod)
+        return mod
+    cxx = types.ModuleType("compressai._CXX")
+    cxx.pmf_to_quantized_cdf = None
+    return cxx
+
+
+def load_models():
+    """-> namespace with the reference's own model classes (``Cheng2020AnchorCheckerboardGMMv2``,
+    ``Elic2022GMM``) and latent codecs, imported from the files under /root/reference unmodified
+    (models/ckbd_gmm.py:61-141, models/elic_gmm.py:64-235)."""
+    em, lc = load()
+    reg = sys.modules["compressai.registry"]
+    reg.register_model = lambda name: (lambda cls: cls)
+    for sub in ("layers", "models"):
+        if f"compressai.{sub}" not in sys.modules:
+            _pkg(f"compressai.{sub}", REF_ROOT / "compressai" / sub)
+    layers = importlib.import_module("compressai.layers.layers")
+    gdn = importlib.import_module("compressai.layers.gdn")
+    lpk = sys.modules["compressai.layers"]
+    for k in dir(layers):
+        if not k.startswith("_"):
+            setattr(lpk, k, getattr(layers, k))
+    lpk.GDN = gdn.GDN
+    ems = sys.modules["compressai.entropy_models"]
+    for k in ("EntropyBottleneck", "EntropyModel", "GaussianConditional", "GaussianMixtureConditional"):
+        setattr(ems, k, getattr(em, k))
+    lcs = sys.modules["compressai.latent_codecs"]
+    for modname, names in (("base", ["LatentCodec"]), ("gaussian_conditional", ["GaussianConditionalLatentCodec"]),
+                           ("gaussian_mixture_conditional", ["GaussianMixtureConditionalLatentCodec"]),
+                           ("hyper", ["HyperLatentCodec"]), ("hyperprior", ["HyperpriorLatentCodec"]),
+                           ("checkerboard", ["CheckerboardLatentCodec"]), ("channel_groups", ["ChannelGroupsLatentCodec"])):
+        m = importlib.import_module(f"compressai.latent_codecs.{modname}")
+        for n in names:
+            setattr(lcs, n, getattr(m, n))
+    ns = types.SimpleNamespace(entropy_models=em, latent_codecs=lcs, layers=lpk)
+    ns.ckbd_gmm = importlib.import_module("compressai.models.ckbd_gmm")
+    ns.elic_gmm = importlib.import_module("compressai.models.elic_gmm")
+    ns.Cheng2020AnchorCheckerboardGMMv2 = ns.ckbd_gmm.Cheng2020AnchorCheckerboardGMMv2
+    ns.Elic2022GMM = ns.elic_gmm.Elic2022GMM
+    return ns
+
+
 def load():
     """-> (entropy_models module, gaussian_mixture_conditional latent-codec module) of the reference."""
     if "compressai" in sys.modules and not getattr(sys.modules["compressai"], "_flashgmm_ref_stub", False):
@@ -44,8 +97,7 @@ def load():
         root._flashgmm_ref_stub = True
         root.ans = ref.load_ans()
         sys.modules["compressai.ans"] = root.ans
-        cxx = types.ModuleType("compressai._CXX")
-        cxx.pmf_to_quantized_cdf = None
+        cxx = _load_cxx()
         sys.modules["compressai._CXX"] = cxx
         root._CXX = cxx
         root.available_entropy_coders = lambda: ["ans"]
