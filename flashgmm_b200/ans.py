@@ -179,14 +179,40 @@ def table_decode(encoded: bytes, indexes, cdfs, cdfs_sizes, offsets) -> np.ndarr
     return out
 
 
+def scalar_gaussian_encode(symbols, scales, mode=None) -> bytes:
+    """``RansEncoder.encode_with_indexes(symbols, scales, max_value)`` (rans_interface.cpp:401-456): zero-mean
+    Gaussian of scale ``scales[i]`` per symbol through the SCALAR libm approximations. Host routine (the
+    reference's is scalar CPU code and no shipped model calls it); parity unpinned across hosts."""
+    sym = np.ascontiguousarray(symbols, np.int32)
+    sc = np.ascontiguousarray(scales, np.float32)
+    if sym.ndim != 1 or sym.shape != sc.shape:
+        raise ValueError("symbols / scales must be 1-D and the same length")
+    mode = get_approx_mode() if mode is None else mode
+    cap = max(64, sym.size * 5 + 64)
+    out = np.empty(cap, np.uint8)
+    n_out = C.c_size_t(0)
+    _lib.check(_lib.lib().flashgmm_scalar_gaussian_encode(sym.ctypes.data, sc.ctypes.data, sym.size, mode,
+                                                          out.ctypes.data, cap, C.byref(n_out)))
+    return out[: n_out.value].tobytes()
+
+
+def scalar_gaussian_decode(encoded: bytes, scales, max_bs_value: int, mode=None) -> np.ndarray:
+    """``RansDecoder.decode_with_indexes(encoded, scales, max_bs_value)`` (rans_interface.cpp:690-764)."""
+    sc = np.ascontiguousarray(scales, np.float32)
+    buf = np.frombuffer(encoded, np.uint8)
+    out = np.empty(sc.size, np.int32)
+    mode = get_approx_mode() if mode is None else mode
+    _lib.check(_lib.lib().flashgmm_scalar_gaussian_decode(buf.ctypes.data, buf.size, sc.ctypes.data, sc.size, mode,
+                                                          int(max_bs_value), out.ctypes.data))
+    return out
+
+
 class RansEncoder:
     """rans_interface.cpp:986-1004."""
 
     def encode_with_indexes(self, symbols, indexes, cdfs=None, cdfs_sizes=None, offsets=None):
-        if cdfs is None:
-            raise NotImplementedError(
-                "encode_with_indexes(symbols, scales, max_value): the scalar single-Gaussian coder "
-                "(rans_interface.cpp:401-456) evaluates glibc expf on the CPU and is not part of the B200 path")
+        if cdfs_sizes is None:            # the (symbols, scales, max_value) overload, rans_interface.cpp:600-607
+            return scalar_gaussian_encode(symbols, indexes)
         return table_encode(symbols, indexes, cdfs, cdfs_sizes, offsets)
 
     def encode_with_indexes_gmm(self, symbols, scales, means, weights, max_value=0):
@@ -201,10 +227,8 @@ class RansDecoder:
         self._pos = 0
 
     def decode_with_indexes(self, encoded, indexes, cdfs=None, cdfs_sizes=None, offsets=None):
-        if cdfs is None:
-            raise NotImplementedError(
-                "decode_with_indexes(encoded, scales, max_bs_value): scalar single-Gaussian coder "
-                "(rans_interface.cpp:690-764) is not part of the B200 path")
+        if cdfs_sizes is None:            # the (encoded, scales, max_bs_value) overload, rans_interface.cpp:690-764
+            return scalar_gaussian_decode(encoded, indexes, int(cdfs)).tolist()
         return table_decode(encoded, indexes, cdfs, cdfs_sizes, offsets).tolist()
 
     def decode_with_indexes_gmm(self, encoded, scales, means, weights, max_bs_value):

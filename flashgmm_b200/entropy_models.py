@@ -565,6 +565,9 @@ class GaussianMixtureConditional(_TableModel):
 
     y_q = None
     y_p = None
+    # test hook: a list here receives ("enc" | "dec", per-image (symbols, scales, means, weights) views, abs_max list)
+    # for every coding call, so that a checker can replay the same tensors through the reference
+    trace = None
 
     # -- compress / decompress glue on the device (csrc/gmm_prologue.cu), B images per launch -------
     def _check_coding_args(self, *tensors):
@@ -636,6 +639,8 @@ class GaussianMixtureConditional(_TableModel):
             self.y_q = symbols
         else:
             self.y_p = symbols
+        if self.trace is not None:
+            self.trace.append(("enc", [(symbols, sc, mu, w)], list(abs_max)))
         rv = self.entropy_coder._encoder.encode_with_indexes_gmm(symbols, sc, mu, w, abs_max[0] + 1)
         return (rv, abs_max[0], bitmap[0]), y_quantized
 
@@ -649,6 +654,8 @@ class GaussianMixtureConditional(_TableModel):
         y = y.contiguous()
         y_quantized, bitmap, bitmap_h, abs_max = self._scan(y)
         per_image = self._gather(y_quantized, scales, means, weights, bitmap, bitmap_h.sum(1).tolist())
+        if self.trace is not None:
+            self.trace.append(("enc", per_image, list(abs_max)))
         own = session is None
         if own:
             session = EncodeSession()
@@ -671,6 +678,8 @@ class GaussianMixtureConditional(_TableModel):
         symbols = self.entropy_coder._decoder.decode_with_indexes_gmm(strings, sc, mu, w, abs_max + 1)
         self.y_q = None
         symbols = symbols.to(device=dev, dtype=torch.int32).contiguous()
+        if self.trace is not None:
+            self.trace.append(("dec", [(symbols, sc, mu, w)], [int(abs_max)]))
         return self._scatter(symbols, bitmap, n_kept, (1, bitmap.size(1), scales.size(2), scales.size(3)))
 
     def decompress_batch(self, items: Sequence[Tuple], scales, means, weights) -> Tensor:
@@ -696,9 +705,11 @@ class GaussianMixtureConditional(_TableModel):
         streams = [(items[b][0], sc, mu, w, int(items[b][1]) + 1) for b, (_s, sc, mu, w) in enumerate(per_image)]
         live = [b for b in range(B) if n_kept[b] > 0]
         outs = _batch.decode_batch([streams[b] for b in live]) if live else []
-        total = sum(int(o.numel()) for o in outs)
+        if self.trace is not None:
+            it = iter(outs)
+            self.trace.append(("dec", [(next(it) if n_kept[b] > 0 else None, *per_image[b][1:]) for b in range(B)],
+                               [int(items[b][1]) for b in range(B)]))
         symbols = torch.cat(outs) if len(outs) > 1 else (outs[0] if outs else None)
-        assert symbols is None or symbols.numel() == total
         self.y_q = None
         return self._scatter(symbols, bitmap.contiguous(), n_kept, (B, bitmap.size(1), scales.size(2), scales.size(3)))
 

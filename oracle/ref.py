@@ -107,6 +107,12 @@ class RefWorker:
         return self.call("table_decode", encoded=encoded, indexes=indexes, cdfs=cdfs,
                          cdf_sizes=cdf_sizes, offsets=offsets)
 
+    def scalar_encode(self, symbols, scales, max_value=0):
+        return self.call("scalar_encode", symbols=symbols, scales=scales, max_value=max_value)
+
+    def scalar_decode(self, encoded, scales, max_bs_value):
+        return self.call("scalar_decode", encoded=encoded, scales=scales, max_bs_value=max_bs_value)
+
     def close(self):
         try:
             self.p.stdin.close()

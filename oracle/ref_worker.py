@@ -66,6 +66,12 @@ def main():
                                         [list(map(int, r)) for r in kw["cdfs"]],
                                         list(map(int, kw["cdf_sizes"])), list(map(int, kw["offsets"])))
             return np.asarray(o, np.int32)
+        if op == "scalar_encode":   # single-Gaussian overload, rans_interface.cpp:401-456, 600-607
+            return bytes(enc.encode_with_indexes(list(map(int, kw["symbols"])), list(map(float, kw["scales"])),
+                                                 int(kw.get("max_value", 0))))
+        if op == "scalar_decode":   # rans_interface.cpp:690-764
+            return np.asarray(dec.decode_with_indexes(kw["encoded"], list(map(float, kw["scales"])),
+                                                      int(kw["max_bs_value"])), np.int32)
         if op == "buffered":      # BufferedRansEncoder: a list of ("table", ...) / ("gmm", ...) pushes, one flush
             be = ans.BufferedRansEncoder()
             for kind, a in kw["pushes"]:

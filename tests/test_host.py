@@ -284,3 +284,38 @@ def test_approx_mode_env_parsing(monkeypatch):
     monkeypatch.delenv("APPROX_MODE")
     ans._mode = None
     assert ans.get_approx_mode() == 0
+
+
+# ---- a14: scalar single-Gaussian search coder (host, libm) ------------------------------------------------
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_scalar_gaussian_coder_matches_the_reference_built_here(mode, ref_available):
+    """RansEncoder.encode_with_indexes(symbols, scales, max) / RansDecoder.decode_with_indexes(encoded, scales, max)
+    (rans_interface.cpp:401-456, 690-764). Parity is unpinned across hosts (glibc expf): the check is against the
+    reference compiled on THIS machine, through its own pybind overloads."""
+    if not ref_available:
+        pytest.skip("compiled reference (oracle/_ref) not present")
+    from oracle import ref
+    from flashgmm_b200 import ans
+
+    rng = np.random.default_rng(100 + mode)
+    n = 20000
+    scales = (0.11 + 6.0 * rng.random(n) ** 2).astype(np.float32)
+    sym = np.round(rng.standard_normal(n) * scales).astype(np.int32)
+    sym[:6] = [0, 900, -900, 70000, -(2 ** 31), 2 ** 31 - 1]            # bypass payloads of 0..8 nibbles
+    R = 64
+    inside = np.abs(sym) <= R
+    with ref.RefWorker(mode=mode) as w:
+        want = w.scalar_encode(sym, scales)
+        got = ans.scalar_gaussian_encode(sym, scales, mode)
+        assert got == want
+        dec_ref = w.scalar_decode(want, scales, R)
+    dec = ans.scalar_gaussian_decode(got, scales, R, mode)
+    assert np.array_equal(dec, dec_ref)
+    assert np.array_equal(dec[inside], sym[inside])
+    # the pybind-shaped overloads
+    ans.set_approx_mode(mode)
+    try:
+        assert ans.RansEncoder().encode_with_indexes(sym.tolist(), scales.tolist(), R) == want
+        assert ans.RansDecoder().decode_with_indexes(want, scales.tolist(), R) == dec_ref.tolist()
+    finally:
+        ans.set_approx_mode(0)

@@ -99,3 +99,117 @@ def test_latent_codec_chunks_and_softmax():
     torch.testing.assert_close(ww.reshape(1, 4, 5, 2, 3).sum(1), torch.ones(1, 5, 2, 3))
     with pytest.raises(AssertionError):
         fg.GaussianMixtureConditionalLatentCodec(K=4, quantizer="ste")
+
+
+# ---- the model replicas (tests/gmm_models.py) against the reference's own classes (build container only) ----
+def _ref_models():
+    from oracle import ref_py
+
+    if not ref_py.available():
+        pytest.skip("/root/reference is not present on this machine")
+    return ref_py.load_models()
+
+
+SMALL = {"Cheng2020AnchorCheckerboardGMMv2": dict(N=32, K=4), "Elic2022GMM": dict(N=32, M=144, K=4)}
+
+
+@pytest.mark.parametrize("name", sorted(SMALL))
+def test_replicas_have_the_reference_state_dict_and_seeded_weights(name):
+    import gmm_models as gm
+
+    ns = _ref_models()
+    torch.manual_seed(0)
+    ref = getattr(ns, name)(**SMALL[name]).eval()
+    torch.manual_seed(0)
+    mine = getattr(gm, name)(**SMALL[name]).eval()
+    for stage in ("init", "updated"):
+        a, b = ref.state_dict(), mine.state_dict()
+        assert list(a.keys()) == list(b.keys())
+        for k in a:
+            assert a[k].shape == b[k].shape and torch.equal(a[k], b[k]), (stage, k)
+        ref.update()
+        mine.update()
+    x = torch.rand(1, 3, 64, 64)
+    with torch.no_grad():
+        y = ref.g_a(x)
+        assert torch.equal(y, mine.g_a(x)) and torch.equal(ref.g_s(y), mine.g_s(y))
+
+
+@pytest.mark.parametrize("name", sorted(SMALL))
+@pytest.mark.parametrize("updated", [False, True])
+def test_reference_checkpoints_load_strict(name, updated):
+    """state dicts produced by the REFERENCE's module, before and after net.update(), load with
+    strict=True (the 64-entry scale table and the CDF buffers are resized on load)."""
+    import gmm_models as gm
+
+    ns = _ref_models()
+    torch.manual_seed(3)
+    ref = getattr(ns, name)(**SMALL[name]).eval()
+    if updated:
+        ref.update()
+    sd = ref.state_dict()
+    torch.manual_seed(4)
+    mine = getattr(gm, name)(**SMALL[name]).eval()
+    mine.load_state_dict(sd, strict=True)
+    for k, v in mine.state_dict().items():
+        assert torch.equal(v, sd[k]), k
+    gmc = next(m for m in mine.modules() if isinstance(m, fg.GaussianMixtureConditional))
+    assert gmc._offset.numel() == (64 if updated else 0)
+    # and the other way round: what this package saves loads into the reference's model
+    torch.manual_seed(5)
+    back = getattr(ns, name)(**SMALL[name]).eval()
+    back.load_state_dict(mine.state_dict(), strict=True)
+
+
+@pytest.mark.parametrize("name", sorted(SMALL))
+def test_mount_on_the_reference_model_tree(name):
+    """mount() swaps the entropy models and rebinds the codecs' coding methods on the reference's OWN instances;
+    state_dict keys and values, and forward's module tree, are untouched."""
+    ns = _ref_models()
+    torch.manual_seed(0)
+    net = getattr(ns, name)(**SMALL[name]).eval()
+    net.update()
+    before = {k: v.clone() for k, v in net.state_dict().items()}
+    fg.mount(net)
+    after = net.state_dict()
+    assert list(before.keys()) == list(after.keys())
+    for k in before:
+        assert torch.equal(before[k], after[k]), k
+    kinds = {type(m).__name__: type(m).__module__ for m in net.modules()}
+    assert kinds["GaussianMixtureConditional"].startswith("flashgmm_b200")
+    assert kinds["EntropyBottleneck"].startswith("flashgmm_b200")
+    assert kinds["CheckerboardLatentCodec"].startswith("compressai")          # identity kept, methods rebound
+    ck = next(m for m in net.modules() if type(m).__name__ == "CheckerboardLatentCodec")
+    assert ck.compress.__func__ is fg.CheckerboardLatentCodec.compress
+    assert ck.latent_codec["y"].gaussian_mixture_conditional is ck.y.gaussian_mixture_conditional
+    hp = net.latent_codec
+    assert hp.latent_codec["hyper"].entropy_bottleneck is hp.hyper.entropy_bottleneck
+    # checkerboard (un)embedding of this package == the reference's (data movement only)
+    t = torch.arange(2 * 3 * 5 * 8, dtype=torch.float32).reshape(2, 3, 5, 8)
+    ref_ck = ns.latent_codecs.CheckerboardLatentCodec(forward_method="onepass")
+    for parity in ("even", "odd"):
+        ref_ck.anchor_parity = parity
+        mine = fg.CheckerboardLatentCodec(anchor_parity=parity, forward_method="onepass")
+        assert torch.equal(mine.unembed(t), ref_ck.unembed(t))
+        assert torch.equal(mine.embed(ref_ck.unembed(t)), t)
+    # a mounted model still refuses CPU tensors on the coding path (no CPU fallback)
+    with pytest.raises(RuntimeError):
+        net.compress(torch.rand(1, 3, 64, 64))
+
+
+def test_pmf_to_quantized_cdf_matches_the_reference_extension():
+    from oracle import ref_py
+    from flashgmm_b200.entropy_models import pmf_to_quantized_cdf
+
+    if not ref_py.available():
+        pytest.skip("/root/reference is not present on this machine")
+    cxx = ref_py._load_cxx()
+    if cxx.pmf_to_quantized_cdf is None:
+        pytest.skip("oracle/_ref/_CXX.so not built")
+    rng = np.random.default_rng(0)
+    for n in (2, 3, 17, 64, 300):
+        for sharp in (0.5, 3.0, 12.0):
+            p = rng.random(n).astype(np.float32) ** sharp
+            p[rng.integers(0, n)] += 1.0
+            p = (p / p.sum()).astype(np.float32)
+            assert pmf_to_quantized_cdf(p.tolist(), 16) == list(cxx.pmf_to_quantized_cdf(p.tolist(), 16))

@@ -232,7 +232,7 @@ def test_compress_glue_kernels_match_the_tensor_ops(shape):
     assert bitmap.dtype == torch.int64 and torch.equal(bitmap, want_bitmap)
     assert torch.equal(y_q, yq)
     assert torch.equal(m.y_q, want_sym)
-    sym, a, b, c = m._kept_planes(yq, sc, mu, w, want_bitmap, len(nz))
+    ((sym, a, b, c),) = m._gather(yq, sc, mu, w, want_bitmap.reshape(1, -1).contiguous(), [len(nz)])
     assert torch.equal(sym, want_sym)
     for got, want in ((a, want_sc), (b, want_mu), (c, want_w)):
         assert got.shape == want.shape and got.stride() == (1, got.shape[0]) and torch.equal(got, want)
@@ -241,3 +241,49 @@ def test_compress_glue_kernels_match_the_tensor_ops(shape):
     m2 = fg.GaussianMixtureConditional(K=4).cuda()
     y_hat = m2.decompress(bts, abs_max, bitmap.cpu(), sc, mu, w)      # bitmap may arrive on the CPU
     assert y_hat.shape == y.shape and torch.equal(y_hat, yq)
+
+
+def test_batched_glue_equals_per_image_glue():
+    """B images per launch (scan / gather / scatter): image b's symbols, parameter views, abs_max, bitmap and
+    bytes are those of coding image b alone; ragged kept-channel counts, one image with nothing kept."""
+    B, Cc, H, W = 5, 24, 8, 6
+    g = torch.Generator().manual_seed(77)
+    y = (torch.randn((B, Cc, H, W), generator=g) * 4).cuda()
+    y[0, ::2] *= 0.01
+    y[2] *= 0.001                                       # image 2: every channel rounds to zero
+    y[3, 5:] *= 0.01
+    y[4, 0, 0, 0] = 300.7
+    sc = (torch.rand((B, 4 * Cc, H, W), generator=g) * 3 + 0.05).cuda()
+    mu = torch.randn((B, 4 * Cc, H, W), generator=g).cuda()
+    w = torch.softmax(torch.randn((B, 4, Cc, H, W), generator=g), 1).reshape(B, 4 * Cc, H, W).cuda()
+    m = fg.GaussianMixtureConditional(K=4).cuda()
+    items, y_q = m.compress_batch(y, sc, mu, w)
+    assert len(items) == B and torch.equal(y_q, torch.round(y))
+    for b in range(B):
+        one = fg.GaussianMixtureConditional(K=4).cuda()
+        (bts, abs_max, bitmap), yq1 = one.compress(y[b:b + 1].contiguous(), sc[b:b + 1], mu[b:b + 1], w[b:b + 1])
+        assert items[b][0] == bts and items[b][1] == abs_max and torch.equal(items[b][2], bitmap)
+        assert torch.equal(yq1, y_q[b:b + 1])
+    assert items[2][0] == bytes.fromhex("0000008000000000") and int(items[2][2].sum()) == 0
+    y_hat = m.decompress_batch(items, sc, mu, w)
+    assert torch.equal(y_hat, torch.round(y))
+    # bitmaps arriving on the CPU (from a container), tuples or lists
+    cpu_items = [(it[0], it[1], it[2].cpu()) for it in items]
+    assert torch.equal(m.decompress_batch(cpu_items, sc, mu, w), torch.round(y))
+
+
+def test_bounds_are_read_from_the_loaded_buffers():
+    """a checkpoint whose bounds differ from the constructor's must be honoured."""
+    m = fg.GaussianMixtureConditional(K=2).cuda().eval()
+    sd = m.state_dict()
+    sd["lower_bound_scale.bound"] = torch.tensor([0.5])
+    sd["likelihood_lower_bound.bound"] = torch.tensor([1e-3])
+    m.load_state_dict(sd)
+    x = torch.tensor([[[[0.0, 9.0]]]]).cuda()
+    sc = torch.full((1, 2, 1, 2), 0.2).cuda()
+    mu = torch.zeros(1, 2, 1, 2).cuda()
+    w = torch.full((1, 2, 1, 2), 0.5).cuda()
+    _, lik = m(x, sc, mu, w)
+    want = torch_likelihood(x, sc, mu, w, 2, scale_bound=0.5).clamp_min(1e-3)
+    close(lik, want.cpu().numpy())
+    assert float(lik[0, 0, 0, 1]) == pytest.approx(1e-3)
