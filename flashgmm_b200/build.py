@@ -20,7 +20,7 @@ INCLUDE = PKG.parent / "include"
 LIB = PKG / "libflashgmm_b200.so"
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-O3,-fno-strict-aliasing", "-I", str(INCLUDE)]
+COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-O3,-fno-strict-aliasing,-g1", "-I", str(INCLUDE)]
 
 # (source, extra flags). Kernel TUs of the bit-exact path are built with FMA
 # contraction off on top of the explicit _rn intrinsics; host-heavy TUs get AVX2.

@@ -283,7 +283,15 @@ inline void pop_rows(RansDecoder64& dec, const uint16_t* row, int64_t rs, int32_
             v = (int32_t)dec.bypass_raw();
         } else {
             uint32_t st, fr;
-            v = search_row(row, plan, cum, &st, &fr);
+            if (__builtin_expect(i + 1 == cnt && 16 * plan.nvec > rs, 0)) {
+                // the vector search reads whole 16-entry vectors: the last row of a table may end before the
+                // last vector does (rows are padded to 8 entries), so it is searched in a padded copy
+                uint16_t last[16 * 4 + 16] = {0};
+                memcpy(last, row, (size_t)rs * sizeof(uint16_t));
+                v = search_row(last, plan, cum, &st, &fr);
+            } else {
+                v = search_row(row, plan, cum, &st, &fr);
+            }
             dec.advance(st, fr);
         }
         out[i] = v;

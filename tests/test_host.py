@@ -319,3 +319,36 @@ def test_scalar_gaussian_coder_matches_the_reference_built_here(mode, ref_availa
         assert ans.RansDecoder().decode_with_indexes(want, scales.tolist(), R) == dec_ref.tolist()
     finally:
         ans.set_approx_mode(0)
+
+
+def test_pop_table_does_not_read_past_the_last_row():
+    """Regression (round 2): the 16-entry vector search over-read the end of the table by up to 16 bytes (rows are
+    padded to 8 entries); with the table ending at a page boundary that was a segfault. The table is placed so that
+    its last byte is the last byte of a readable page followed by a PROT_NONE page."""
+    import mmap
+
+    R = 10                                           # 21 candidates -> 2 vectors = 32 entries, row stride 24
+    sym, sg, mu, w = synth.gmm_numpy(3000, seed=77, sigma_span=1.0, mean_scale=1.0)
+    core = np.clip(sym, -R + 1, R - 1)
+    enc = port.gmm_encode(core, sg, mu, w, 0)
+    L = _lib.lib()
+    rs = L.flashgmm_gmm_table_row_stride(R)
+    assert rs == 24
+    T = make_rows(port.gmm_cdf_table(sg, mu, w, R, 0), R)
+    nbytes = T.nbytes
+    page = mmap.PAGESIZE
+    span = (nbytes + page - 1) // page * page
+    mm = mmap.mmap(-1, span + page)
+    base = C.addressof(C.c_char.from_buffer(mm))
+    libc = C.CDLL(None, use_errno=True)
+    libc.mprotect.argtypes = [C.c_void_p, C.c_size_t, C.c_int]
+    assert libc.mprotect(base + span, page, 0) == 0                        # PROT_NONE guard page
+    start = base + span - nbytes
+    C.memmove(start, T.ctypes.data, nbytes)
+    out = np.empty(core.size, np.int32)
+    buf = np.frombuffer(enc, np.uint8)
+    try:
+        _lib.check(L.flashgmm_rans_pop_table(buf.ctypes.data, buf.size, start, rs, core.size, R, out.ctypes.data))
+    finally:
+        libc.mprotect(base + span, page, 3)
+    assert np.array_equal(out, core)

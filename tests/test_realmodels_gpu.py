@@ -104,10 +104,10 @@ def check_against_reference(trace, strings_by_pass, worker, kind):
                 assert item[0] == bytes.fromhex("0000008000000000")
                 continue
             if kind == "enc":
-                want = worker.gmm_encode(sym, sc, mu, w)
+                want, _dt = worker.gmm_encode(sym, sc, mu, w)
                 assert item[0] == want, f"stream of image {b}: bytes differ from the compiled reference"
             else:
-                want = worker.gmm_decode(item[0], sc, mu, w, abs_max[b] + 1)
+                want, _dt = worker.gmm_decode(item[0], sc, mu, w, abs_max[b] + 1)
                 assert np.array_equal(sym, want), f"image {b}: decoded symbols differ from the compiled reference"
             n_checked += 1
     return n_checked
