@@ -53,6 +53,19 @@ def elic_stream_sizes():
     return sizes
 
 
+def common_config(args):
+    """The `config` both arms print (the driver compares them): what is coded per step, not how."""
+    B = args.images_per_step
+    nsym = sum(elic_stream_sizes())
+    return {"workload": f"elic2022gmm_768x512 x{B} images/step: 10 GMM streams/image, 491520 symbols/image, K=4, "
+                        f"APPROX_MODE={args.mode}",
+            "step": f"encode {10 * B} streams + decode {10 * B} streams ({B} images) per GPU; every step codes its images "
+                    "completely, bytes identical to the reference's single-stream coder",
+            "images_per_step": B, "approx_mode": args.mode, "decode_order": args.decode_order,
+            "l2": f"inputs rotate over {N_SETS} batches of {B} images = {N_SETS * B * nsym * 52 / 1e6:.0f} MB "
+                  "(one batch alone exceeds the 126 MB L2)"}
+
+
 def emit(obj):
     print(json.dumps(obj), flush=True)
 
@@ -154,6 +167,7 @@ def bind_to_gpu_cpus(local_rank):
 
 def run_b200(args):
     import ctypes as C
+    import threading
 
     import torch
     import torch.distributed as dist
@@ -161,6 +175,7 @@ def run_b200(args):
     from flashgmm_b200 import _lib, shard, synth
     from flashgmm_b200.batch import DecodeJob, EncodeJob
 
+    _lib.want_more_hw_queues(32)          # before the CUDA context exists (read at context creation)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -179,8 +194,11 @@ def run_b200(args):
 
     B = args.images_per_step
     sizes = elic_stream_sizes()
+    n_pass = len(sizes)
     nsym = sum(sizes)
     mode = args.mode
+    order = args.decode_order
+    depth = max(1, args.pipeline_depth)
     # two rotating batches of B images; one batch alone (B x 25.6 MB) already exceeds L2 for B >= 5
     batches = [[make_image(torch, synth, 1000 * rank + 100 * s + i, dev) for i in range(B)] for s in range(N_SETS)]
     radii = [[[int(st[0].abs().max().item()) + 2 for st in img] for img in bt] for bt in batches]
@@ -190,16 +208,40 @@ def run_b200(args):
     def flat(bt):
         return [st for img in bt for st in img]
 
-    def jobs_for(bts):
-        enc = [EncodeJob(flat(bt), mode) for bt in bts]
-        dec = [DecodeJob([(sg, mu, w, R) for img, rr in zip(bt, rb) for (_, sg, mu, w), R in zip(img, rr)], mode)
-               for bt, rb in zip(bts, radii)]
-        return enc, dec
+    class Lane:
+        """One host thread's share of the pipeline: its own ctx (a ctx serialises its calls) and pre-bound jobs.
+        A step = encode every stream of the batch in one call (the encoder knows all of y up front), then decode
+        pass by pass: pass p's call carries the B streams of pass p, and pass p+1 is not issued before it returns
+        (a real decoder forms pass p+1's parameters from pass p's symbols)."""
 
-    def step(enc, dec, i):
-        k = i % N_SETS
-        streams = enc[k].run()
-        return dec[k].run(streams), streams
+        def __init__(self, bts, ctx):
+            self.ctx = ctx
+            self.enc = [EncodeJob(flat(bt), mode, ctx=self.ctx) for bt in bts]
+            self.dec = []
+            for bt, rb in zip(bts, radii):
+                per_stream = [[(sg, mu, w, R) for (_, sg, mu, w), R in zip(img, rr)] for img, rr in zip(bt, rb)]
+                if order == "pass-sequential":
+                    self.dec.append([DecodeJob([per_stream[i][p] for i in range(B)], mode, ctx=self.ctx) for p in range(n_pass)])
+                else:
+                    self.dec.append([DecodeJob([st for img in per_stream for st in img], mode, ctx=self.ctx)])
+
+        def encode(self, k):
+            return self.enc[k].run()
+
+        def decode(self, k, streams):
+            """-> decoded symbols in flat (image, pass) order"""
+            if order != "pass-sequential":
+                return self.dec[k][0].run(streams)
+            outs = [None] * (B * n_pass)
+            for p, job in enumerate(self.dec[k]):
+                for i, o in enumerate(job.run([streams[i * n_pass + p] for i in range(B)])):
+                    outs[i * n_pass + p] = o
+            return outs
+
+        def step(self, i):
+            k = i % N_SETS
+            streams = self.encode(k)
+            return self.decode(k, streams), streams
 
     def check(outs, bt):
         for o, (sym, *_r) in zip(outs, flat(bt)):
@@ -212,7 +254,31 @@ def run_b200(args):
             dist.barrier()
             torch.cuda.synchronize()
 
-    def timed(enc, dec, steps, profile=False):
+    def run_steps(lanes, steps):
+        """`steps` steps over the lanes: lane j takes steps j, j + D, ... (independent images); with D > 1 one
+        batch's encode and another's pass-sequential decode overlap on the GPU."""
+        if len(lanes) == 1:
+            for i in range(steps):
+                lanes[0].step(i)
+            return
+        errs = []
+
+        def work(j):
+            try:
+                torch.cuda.set_device(local)
+                for i in range(j, steps, len(lanes)):
+                    lanes[j].step(i)
+            except BaseException as e:                       # noqa: BLE001
+                errs.append(e)
+        th = [threading.Thread(target=work, args=(j,)) for j in range(len(lanes))]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        if errs:
+            raise errs[0]
+
+    def timed(lanes, steps, profile=False):
         barrier()
         if profile:
             L.flashgmm_profile_reset()
@@ -221,8 +287,7 @@ def run_b200(args):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         e0.record()
-        for i in range(steps):
-            step(enc, dec, i)
+        run_steps(lanes, steps)
         e1.record()
         torch.cuda.synchronize()
         wall = time.perf_counter() - t0
@@ -237,16 +302,20 @@ def run_b200(args):
 
     W = max(args.warmup, 3)
     # ---- device-resident arm ----
-    enc_d, dec_d = jobs_for(batches)
-    for i in range(W):
-        outs, streams = step(enc_d, dec_d, i)
-        check(outs, batches[i % N_SETS])
+    ctxs = [_lib.ctx(local) if j == 0 else _lib.new_ctx(local) for j in range(depth)]
+    lanes_d = [Lane(batches, ctxs[j]) for j in range(depth)]
+    for ln in lanes_d:
+        for i in range(W if ln is lanes_d[0] else 2):
+            outs, streams = ln.step(i)
+            check(outs, batches[i % N_SETS])
     bits = sum(s.size for s in streams) * 8 / (nsym * B)
     sampler = start_clock_sampler(local) if rank == 0 else None
-    secs, launches = timed(enc_d, dec_d, args.steps)
+    secs, launches = timed(lanes_d, args.steps)
     clocks = stop_clock_sampler(sampler)
-    # per-kernel CUDA-event timing in a second pass (events add host work to every launch)
-    timed(enc_d, dec_d, max(2, args.steps // 4), profile=True)
+    secs_d1, _ = timed(lanes_d[:1], max(2, args.steps // 2)) if depth > 1 else (secs, 0)
+    steps_d1 = max(2, args.steps // 2) if depth > 1 else args.steps
+    # per-kernel CUDA-event timing in a separate pass on one lane (events add host work to every launch)
+    timed(lanes_d[:1], max(2, args.steps // 4), profile=True)
     prof = {}
     for kind, name in ((0, "gmm_startfreq"), (1, "gmm_cdf_rows"), (4, "gmm_pop_rows"), (5, "gmm_push")):
         ms, n, by = C.c_double(), C.c_uint64(), C.c_double()
@@ -254,42 +323,60 @@ def run_b200(args):
         if n.value:
             prof[name] = dict(ms=ms.value, launches=n.value, bytes=by.value)
 
-    # encode-only / decode-only split on the same inputs (reported beside the headline)
-    bs = [[x.copy() for x in enc_d[k].run()] for k in range(N_SETS)]
+    # encode-only / decode-only split on the same inputs, one lane (reported beside the headline)
+    ln0 = lanes_d[0]
+    bs = [[x.copy() for x in ln0.encode(k)] for k in range(N_SETS)]
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for i in range(args.steps):
-        enc_d[i % N_SETS].run()
+        ln0.encode(i % N_SETS)
     t1 = time.perf_counter()
     for i in range(args.steps):
-        dec_d[i % N_SETS].run(bs[i % N_SETS])
+        ln0.decode(i % N_SETS, bs[i % N_SETS])
     torch.cuda.synchronize()
     t2 = time.perf_counter()
     enc_t, dec_t = (t1 - t0) / args.steps, (t2 - t1) / args.steps
+    # the other decode order beside it, labelled (pass-parallel = all 10 x B streams in ONE call: an upper bound
+    # no real decoder reaches, since pass p+1's parameters need pass p's symbols)
+    other = DecodeJob([(sg, mu, w, R) for img, rr in zip(batches[0], radii[0]) for (_, sg, mu, w), R in zip(img, rr)], mode)
+    other.run(bs[0])
+    t0 = time.perf_counter()
+    for i in range(max(2, args.steps // 2)):
+        other.run(bs[0])
+    torch.cuda.synchronize()
+    dec_parallel_t = (time.perf_counter() - t0) / max(2, args.steps // 2)
+    del other
 
-    # single-image latency (one image's ten streams per call)
+    # single-image latency (one image's ten streams: one encode call, ten dependent decode calls)
     e1j = EncodeJob(batches[0][0], mode)
-    d1j = DecodeJob([(sg, mu, w, R) for (_, sg, mu, w), R in zip(batches[0][0], radii[0][0])], mode)
+    if order == "pass-sequential":
+        d1j = [DecodeJob([(sg, mu, w, R)], mode) for (_, sg, mu, w), R in zip(batches[0][0], radii[0][0])]
+    else:
+        d1j = [DecodeJob([(sg, mu, w, R) for (_, sg, mu, w), R in zip(batches[0][0], radii[0][0])], mode)]
     lat_e, lat_d = [], []
     for i in range(12):
         t0 = time.perf_counter()
         b1 = e1j.run()
         t1 = time.perf_counter()
-        d1j.run(b1)
+        if order == "pass-sequential":
+            for p, job in enumerate(d1j):
+                job.run([b1[p]])
+        else:
+            d1j[0].run(b1)
         t2 = time.perf_counter()
         if i >= 2:
             lat_e.append(t1 - t0)
             lat_d.append(t2 - t1)
+    del e1j, d1j
 
     # ---- end-to-end arm: pinned host inputs, copies inside the timed region ----
     host_batches = [[to_pinned(torch, img) for img in bt] for bt in batches]
-    enc_h = [EncodeJob(flat(bt), mode) for bt in host_batches]
-    dec_h = [DecodeJob([(sg, mu, w, R) for img, rr in zip(bt, rb) for (_, sg, mu, w), R in zip(img, rr)], mode)
-             for bt, rb in zip(host_batches, radii)]
-    for i in range(W):
-        outs, _ = step(enc_h, dec_h, i)
-        check(outs, host_batches[i % N_SETS])
-    secs_e2e, _ = timed(enc_h, dec_h, args.steps)
+    lanes_h = [Lane(host_batches, ctxs[j]) for j in range(depth)]
+    for ln in lanes_h:
+        for i in range(W if ln is lanes_h[0] else 2):
+            outs, _ = ln.step(i)
+            check(outs, host_batches[i % N_SETS])
+    secs_e2e, _ = timed(lanes_h, args.steps)
 
     micro = kernel_microbench(torch, synth, L, _lib, dev, mode) if (world == 1 and not args.no_microbench) else None
 
@@ -326,7 +413,7 @@ def run_b200(args):
                 "traffic": round(dram * per_launch / ALGO_BYTES_PER_SYMBOL[name]) if dram else None,
                 "algorithmic_bytes_per_launch": round(per_launch), "peak_source": peak_src,
                 "avg_launch_us": round(1e3 * p["ms"] / max(1, p["launches"]), 2), "launches": p["launches"],
-                "share_of_gpu_time": round(p["ms"] / max(1e-9, sum(v["ms"] for v in prof.values())), 3),
+                "share_of_summed_kernel_time": round(p["ms"] / max(1e-9, sum(v["ms"] for v in prof.values())), 3),
                 "note": notes[name]}
 
     line = {
@@ -336,18 +423,25 @@ def run_b200(args):
         "ms_per_image": round(1e3 * secs / args.steps / B, 4),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": f"elic2022gmm_768x512 x{B} images/step: 10 GMM streams/image, 491520 symbols/image, K=4, "
-                               f"APPROX_MODE={mode}",
-                   "step": f"encode {10 * B} streams + decode {10 * B} streams ({B} images) per GPU",
-                   "l2": f"inputs rotate over {N_SETS} batches of {B} images = {N_SETS * B * nsym * 52 / 1e6:.0f} MB "
-                         "(one batch alone exceeds the 126 MB L2)",
+        "config": common_config(args),
+        "details": {
                    "bits_per_symbol": round(bits, 3), "search_radius": radii[0][0][-1],
+                   "decode_order": order + (f": {n_pass} dependent decode calls of {B} streams per step (pass p+1 is issued only "
+                                            "after pass p has returned)" if order == "pass-sequential" else
+                                            f": all {n_pass * B} streams in one call (upper bound, not a real decoder)"),
+                   "pipeline_depth": depth,
+                   "pipeline": f"{depth} independent batches in flight (one host thread + ctx each): one batch's encode overlaps "
+                               "another's pass-sequential decode; every step still codes its own 24 images completely",
                    "decode": "device-resident (rows kernel -> pop kernel, one warp per stream)",
                    "encode": "batched startfreq launches -> serial push: the longest streams on host worker threads (records "
                              "come down wave by wave), the rest on the device (push kernel, one warp per stream), "
                              "split by a cost model (FLASHGMM_PUSH)",
                    "host_workers": int(os.environ.get("FLASHGMM_WORKERS", "0")) or min(16, max(1, (os.cpu_count() or 2) - 1)),
                    "host_cores": os.cpu_count(), "cpus_bound_to_gpu_locality": numa_cpus},
+        "value_one_batch_in_flight": round(2 * nsym * B * steps_d1 * world / secs_d1 / 1e6, 2),
+        "decode_pass_parallel_msym_s": round(nsym * B / dec_parallel_t / 1e6, 2),
+        "decode_pass_parallel_ms_per_step": round(1e3 * dec_parallel_t, 4),
+        "encode_ms_per_step": round(1e3 * enc_t, 4), "decode_ms_per_step": round(1e3 * dec_t, 4),
         "encode_ms_per_image": round(1e3 * enc_t / B, 4), "decode_ms_per_image": round(1e3 * dec_t / B, 4),
         "encode_msym_s": round(nsym * B / enc_t / 1e6, 2), "decode_msym_s": round(nsym * B / dec_t / 1e6, 2),
         "latency_single_image_ms": {"encode": round(1e3 * statistics.median(lat_e), 4),
@@ -572,9 +666,7 @@ def run_reference(args):
         "ms_per_step": round(1e3 * secs / args.steps, 3), "ms_per_image": round(1e3 * secs / args.steps / B, 3),
         "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"elic2022gmm_768x512 x{B} images/step: 10 GMM streams/image, 491520 symbols/image, K=4, "
-                               f"APPROX_MODE={mode}",
-                   "step": f"encode {10 * B} streams + decode {10 * B} streams ({B} images)", "host_cores": cores},
+        "config": common_config(args), "details": {"host_cores": cores},
         "cpu_baseline": {"value": val, "unit": "Msymbols/s", "cores": P, "kind": kind,
                          "sample": f"whole batch per step; {P} worker processes (USE_SIMD=1), streams dealt "
                                    "longest-first, tensors resident in the workers"},
@@ -593,6 +685,11 @@ def main():
     ap.add_argument("--images-per-step", type=int, default=24,
                     help="images per step and per GPU (BASELINE.json configs[4] works on 24 images)")
     ap.add_argument("--mode", type=int, default=0, choices=[0, 1, 2], help="APPROX_MODE (reference code numbering)")
+    ap.add_argument("--decode-order", default="pass-sequential", choices=["pass-sequential", "pass-parallel"],
+                    help="pass-sequential (default, what a real decoder can do): one decode call per coding pass, "
+                         "issued after the previous pass has returned; pass-parallel: every stream in one call")
+    ap.add_argument("--pipeline-depth", type=int, default=2,
+                    help="independent batches in flight (host threads, one ctx each); 1 = strictly one after the other")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

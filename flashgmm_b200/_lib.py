@@ -149,5 +149,17 @@ def ctx(device: int = 0):
     return h
 
 
+def new_ctx(device: int = 0):
+    """A further context on ``device`` (own streams, buffers and worker threads): a ctx serialises its calls, so
+    concurrent host threads -- e.g. batch k+1's encode beside batch k's decode -- use one ctx each. Freed at exit."""
+    out = _vp()
+    check(lib().flashgmm_ctx_create(int(device), C.byref(out)))
+    _extra_ctxs.append(out)
+    return out
+
+
+_extra_ctxs: list = []
+
+
 def launch_count() -> int:
     return int(lib().flashgmm_launch_count())

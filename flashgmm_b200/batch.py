@@ -20,7 +20,7 @@ from .ans import _dev_index, _gmm_views, _tensor, get_approx_mode
 class EncodeJob:
     """Pre-bound encode call over fixed tensors (re-usable: no per-call allocation)."""
 
-    def __init__(self, streams: Sequence[Tuple], mode=None):
+    def __init__(self, streams: Sequence[Tuple], mode=None, ctx=None):
         self.mode = get_approx_mode() if mode is None else mode
         self.n_streams = len(streams)
         self.arr = (_lib.Stream * max(1, self.n_streams))()
@@ -44,7 +44,7 @@ class EncodeJob:
             a.n, a.stride_n, a.stride_k = N, sn, sk
             a.bytes, a.bytes_cap = out.ctypes.data, out.size
         self.mem = _lib.MEM_HOST if (self.device is None or self.device.type == "cpu") else _lib.MEM_DEVICE
-        self.ctx = _lib.ctx(_dev_index(self.device if self.device is not None else torch.device("cpu")))
+        self.ctx = ctx if ctx is not None else _lib.ctx(_dev_index(self.device if self.device is not None else torch.device("cpu")))
 
     def run(self) -> List[np.ndarray]:
         """-> per-stream uint8 views of the produced bitstreams (valid until the next run)."""
@@ -63,7 +63,7 @@ class EncodeJob:
 class DecodeJob:
     """Pre-bound decode call: parameters and output tensors fixed, bitstreams per run."""
 
-    def __init__(self, streams: Sequence[Tuple], mode=None):
+    def __init__(self, streams: Sequence[Tuple], mode=None, ctx=None):
         """streams: (scales, means, weights, max_bs_value) per stream."""
         self.mode = get_approx_mode() if mode is None else mode
         self.n_streams = len(streams)
@@ -85,9 +85,11 @@ class DecodeJob:
             a.n, a.stride_n, a.stride_k, a.max_bs_value = N, sn, sk, int(R)
             a.symbols_out = out.data_ptr()
         self.mem = _lib.MEM_HOST if (self.device is None or self.device.type == "cpu") else _lib.MEM_DEVICE
-        self.ctx = _lib.ctx(_dev_index(self.device if self.device is not None else torch.device("cpu")))
+        self.ctx = ctx if ctx is not None else _lib.ctx(_dev_index(self.device if self.device is not None else torch.device("cpu")))
 
     def run(self, bitstreams: Sequence) -> List[torch.Tensor]:
+        if len(bitstreams) != self.n_streams:
+            raise ValueError(f"{len(bitstreams)} bitstreams for a job of {self.n_streams} streams")
         bufs = []
         for i, b in enumerate(bitstreams):
             buf = b if isinstance(b, np.ndarray) else np.frombuffer(b, np.uint8)

@@ -352,3 +352,39 @@ def test_pop_table_does_not_read_past_the_last_row():
     finally:
         libc.mprotect(base + span, page, 3)
     assert np.array_equal(out, core)
+
+
+# ---- f3: the container format ----------------------------------------------------------------------------
+def test_container_roundtrip_and_corruption():
+    import torch
+    from flashgmm_b200 import container
+
+    rng = np.random.default_rng(3)
+    def stream(c):
+        bm = torch.from_numpy((rng.random(c) < 0.7).astype(np.int64))
+        return (rng.integers(0, 256, int(rng.integers(8, 4000)), dtype=np.uint8).tobytes(), int(rng.integers(1, 300)), bm)
+    # one image, the reference's structure (tuples), ELIC-like shapes
+    groups = [16, 16, 32, 64, 192]
+    strings = [stream(g) for g in groups for _ in range(2)] + [[b"zzzz-hyper"]]
+    shape = {"y": [torch.Size([g, 32, 48]) for g in groups], "hyper": torch.Size([8, 12])}
+    blob = container.pack(strings, shape)
+    got, shp, info = container.unpack(blob)
+    assert shp == {"y": tuple((g, 32, 48) for g in groups), "hyper": (8, 12)}
+    assert len(got) == len(strings) and got[-1] == strings[-1]
+    for a, b in zip(got[:-1], strings[:-1]):
+        assert isinstance(a, tuple) and a[0] == b[0] and a[1] == b[1] and torch.equal(a[2], b[2])
+    assert info["images"] == 1 and info["passes"] == 10 and info["payload_bytes"] == sum(len(s[0]) for s in strings[:-1])
+    assert info["total_bytes"] == len(blob) and 0 < info["side_info_bytes"] < 10 * (2 + 2 + 24 + 3) + 1
+    # a batch of 3 images, checkerboard-like
+    strings = [[stream(192) for _ in range(3)] for _ in range(2)] + [[b"a", b"bb", b""]]
+    got, shp, info = container.unpack(container.pack(strings, {"y": (192, 32, 48), "hyper": (8, 12)}))
+    assert info["images"] == 3 and all(isinstance(e, list) and len(e) == 3 for e in got[:-1]) and got[-1] == [b"a", b"bb", b""]
+    for e, f in zip(got[:-1], strings[:-1]):
+        for a, b in zip(e, f):
+            assert a[0] == b[0] and a[1] == b[1] and torch.equal(a[2], b[2])
+    # corruption, truncation, wrong magic / version are refused
+    bad = bytearray(blob)
+    bad[len(bad) // 2] ^= 1
+    for broken in (bytes(bad), blob[:-7], b"XXXX" + blob[4:], blob[:4] + b"\x09" + blob[5:]):
+        with pytest.raises(container.ContainerError):
+            container.unpack(broken)

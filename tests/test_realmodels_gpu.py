@@ -190,6 +190,12 @@ def test_batch_streams_equal_single_image_streams(name, B):
     assert len(enc["strings"]) == n_pass + 1 and all(len(s) == B for s in enc["strings"])
     dec = net.latent_codec.decompress(enc["strings"], enc["shape"])
     assert torch.equal(dec["y_hat"], enc["y_hat"]) and torch.equal(enc["y_hat"], torch.round(y))
+    # through the file container (flashgmm_b200/container.py): bytes -> the same latents
+    from flashgmm_b200 import container
+    blob = container.pack(enc["strings"], enc["shape"])
+    strings2, shape2, info = container.unpack(blob)
+    assert info["images"] == B and info["passes"] == n_pass
+    assert torch.equal(net.latent_codec.decompress(strings2, shape2)["y_hat"], enc["y_hat"])
     for b in range(B):
         one = net.latent_codec.compress(y[b:b + 1].contiguous())
         for p in range(n_pass):
