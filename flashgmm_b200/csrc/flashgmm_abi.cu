@@ -401,6 +401,7 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     const int64_t rec_bytes = windowed ? 4 * (int64_t)kPopWindowWords : 4 * (int64_t)lane_slots;   // record per symbol
     int S = (int)std::min<int64_t>(32, (48 * 1024) / ((12 + max_row_words + 2) * 4));
     if (total_n < 148 * 8 * 32) S = std::min(S, 8);
+    if (windowed) S = kRowsWindowSyms;                       // the windowed kernel's CTA shape is fixed
 
     // ---- work items: (group, symbol range common to the group's streams) ----
     struct Item { int g; int64_t lo, hi, left; int k, ring_prev; };   // k: index within the group; ring_prev: the item whose row buffer it reuses

@@ -298,6 +298,114 @@ gmm_cdf_rows_batched_kernel(const RowsDesc* __restrict__ descs, int n_desc, int 
                              (int64_t)(b - d.first_block), smem_u32, lane_slots);
 }
 
+// ---- decode side, device pop path: the WINDOWED record computed directly (no full row) ----
+// The record the pop kernel reads (gmm_pop.cu) holds 32 consecutive intervals of the symbol's quantised CDF.
+// The first version evaluated the whole row (2R+2 points) and then picked the 32-interval window with the
+// most mass: O(R) work per symbol. Here the window is chosen FROM THE PARAMETERS and only its 33 boundaries
+// are evaluated, so the cost does not grow with the search radius.
+//
+// Why any window is exact: for sane parameters (finite, 0 < sigma <= 65536, w >= 0, sum of weights below the
+// 16-bit wrap) every row is non-decreasing -- the three Phi approximations are monotone over every finite
+// binary32 argument (oracle/check_monotone.c, exhaustive) and subtraction, division by sigma > 0,
+// multiplication by w >= 0, the pairwise sums and the truncation are monotone too -- so the reference's binary
+// search (rans_interface.cpp:826-862) ends on THE interval that contains cum, and a lane of the window that
+// contains cum is that interval. A cum outside the window is "no lane hits": the pop kernel then replays the
+// reference's search literally (pop_slow). Symbols whose parameters are not sane get a blank record (every
+// symbol of theirs takes the literal path). The window choice is therefore only a matter of speed; it uses
+// plain fast arithmetic: centre of [min_k mu_k - 3.9 sigma_k, max_k mu_k + 3.9 sigma_k] over the components
+// that carry weight (miss rate 6e-5 on the synthetic mixture of BASELINE config 4).
+constexpr int kWinThreads = 96;          // 32 symbols x 33 boundaries = 1056 = 96 x 11 points: no idle thread
+constexpr int kWinSyms = 32;
+constexpr int kWinPts = 33;
+
+template <int MODE>
+__global__ void __launch_bounds__(kWinThreads)
+gmm_cdf_window_batched_kernel(const RowsDesc* __restrict__ descs, int n_desc) {
+    __shared__ float prm[12][kWinSyms];                       // sg[4], mu[4], w[4]
+    __shared__ int j0s[kWinSyms];                             // first boundary index of the window, -1 = blank record
+    __shared__ uint32_t T[kWinSyms][kWinPts];                 // stride 33: conflict-free both ways
+    int lo = 0, hi = n_desc - 1;
+    const int b = (int)blockIdx.x;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (descs[mid].first_block <= b) lo = mid; else hi = mid - 1;
+    }
+    const RowsDesc d = descs[lo];
+    const int64_t row0 = (int64_t)(b - d.first_block) * kWinSyms;
+    const int live = (int)min((int64_t)kWinSyms, (int64_t)d.n - row0);
+    const int R = d.R;
+    const int t = (int)threadIdx.x;
+
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int idx = t + kWinThreads * i;                  // 384 = 12 planes x 32 symbols
+        const int plane = idx >> 5, sidx = idx & 31;
+        float v = plane < 4 ? 1.0f : 0.0f;
+        if (sidx < live) {
+            const float* base = plane < 4 ? d.p.scales : (plane < 8 ? d.p.means : d.p.weights);
+            v = __ldg(base + (row0 + sidx) * d.p.stride_n + (plane & 3) * d.p.stride_k);
+        }
+        prm[plane][sidx] = v;
+    }
+    __syncthreads();
+    if (t < kWinSyms) {
+        float lo_x = 3.0e38f, hi_x = -3.0e38f, lo_all = 3.0e38f, hi_all = -3.0e38f;
+        bool sane = true;
+        float wsum[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float sg = prm[k][t], mu = prm[4 + k][t], w = prm[8 + k][t];
+            sane = sane && (sg > 0.0f) && (sg <= 65536.0f) && (w >= 0.0f) && (w <= 2.0f) && (fabsf(mu) <= 1.0e30f);
+            wsum[k] = w;
+            const float a = mu - 3.9f * sg, c = mu + 3.9f * sg;
+            lo_all = fminf(lo_all, a); hi_all = fmaxf(hi_all, c);
+            if (w > 1.0e-3f) { lo_x = fminf(lo_x, a); hi_x = fmaxf(hi_x, c); }
+        }
+        // the largest value any boundary can take is the sum of the weights (same association as the CDF):
+        // it must stay below the 16-bit wrap of the quantiser
+        const float top = __fmul_rn(__fadd_rn(__fadd_rn(wsum[0], wsum[1]), __fadd_rn(wsum[2], wsum[3])), 65535.0f);
+        sane = sane && (top < 65536.0f);
+        if (hi_x < lo_x) { lo_x = lo_all; hi_x = hi_all; }
+        int j0 = -1;
+        if (sane && t < live) {
+            const float centre = fminf(fmaxf(0.5f * (lo_x + hi_x), -3.0e6f), 3.0e6f);
+            const int last = max(0, 2 * R + 1 - 32);          // last admissible first boundary
+            j0 = min(max(__float2int_rn(centre) - 16 + R, 0), last);
+        }
+        j0s[t] = j0;
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int i = 0; i < 11; ++i) {
+        const int id = t + kWinThreads * i;
+        const int sidx = id / kWinPts, l = id - sidx * kWinPts;
+        const int j0 = j0s[sidx];
+        uint32_t e = 65535u;
+        if (j0 >= 0 && j0 + l <= 2 * R + 1) {
+            float mu[4], sg[4], w[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { sg[k] = prm[k][sidx]; mu[k] = prm[4 + k][sidx]; w[k] = prm[8 + k][sidx]; }
+            e = gmm_q16<MODE>(__fsub_rn((float)(j0 + l - R), 0.5f), mu, sg, w);
+        }
+        T[sidx][l] = e;
+    }
+    __syncthreads();
+    uint32_t* dst = d.table32 + row0 * kPopWindowWords;
+    for (int id = t; id < live * kPopWindowWords; id += kWinThreads) {
+        const int sidx = id / kPopWindowWords, q = id - sidx * kPopWindowWords;
+        const int j0 = j0s[sidx];
+        uint32_t v = 0;
+        if (q == 0) v = (uint32_t)((j0 < 0 ? 0 : j0) - R);
+        else if (q >= 4) {
+            const int l = (q - 4) >> 1;
+            const bool ok = j0 >= 0 && j0 + l <= 2 * R;       // interval j0 + l exists in the row
+            const uint32_t a = ok ? T[sidx][l] : 65535u, c = ok ? T[sidx][l + 1] : 65535u;
+            v = (q & 1) ? c - a : a;
+        }
+        __stcs(dst + id, v);
+    }
+}
+
 inline int grid_for(int64_t work, int threads) {
     int64_t b = (work + threads - 1) / threads;
     const int64_t cap = 148LL * 64;   // grid-stride beyond this
@@ -426,6 +534,15 @@ cudaError_t launch_rows_mode(const GmmParamsView& p, int64_t n, int R, uint16_t*
 cudaError_t launch_gmm_cdf_rows_batched(const RowsDesc* descs_d, int n_desc, int total_blocks, int S,
                                         int max_row_words, int lane_slots, int mode, cudaStream_t st) {
     if (n_desc <= 0 || total_blocks <= 0) return cudaSuccess;
+    if (lane_slots == kPopWindowed) {
+        if (S != kRowsWindowSyms) return cudaErrorInvalidValue;      // first_block prefixes are in units of 32 symbols
+        switch (mode) {
+        case MODE_AS: gmm_cdf_window_batched_kernel<MODE_AS><<<total_blocks, kWinThreads, 0, st>>>(descs_d, n_desc); break;
+        case MODE_LOGISTIC: gmm_cdf_window_batched_kernel<MODE_LOGISTIC><<<total_blocks, kWinThreads, 0, st>>>(descs_d, n_desc); break;
+        default: gmm_cdf_window_batched_kernel<MODE_POLYA><<<total_blocks, kWinThreads, 0, st>>>(descs_d, n_desc);
+        }
+        return cudaGetLastError();
+    }
     const size_t smem = (size_t)S * (12 + max_row_words + 2) * 4;    // + bad flag + window base per symbol
     if (smem > 48 * 1024) return cudaErrorInvalidValue;      // callers size S for the widest row
     switch (mode) {

@@ -56,7 +56,8 @@ struct PopDesc {
 constexpr int kPopMaxR = 63;                       // lane-row records: 2R + 1 <= 128 intervals = 4 per lane
 constexpr int kPopWindowed = 1;                    // lane_slots value selecting the windowed record (any R)
 constexpr int kPopWindowWords = 68;                // 272 bytes per symbol
-constexpr int kPopWindowMaxR = 1023;
+constexpr int kPopWindowMaxR = 1 << 20;           // the windowed record costs the same for any search radius
+constexpr int kRowsWindowSyms = 32;                // symbols per CTA of the windowed rows kernel
 inline int gmm_pop_lane_slots(int max_R) {             // 1, 2 or 4 intervals per lane
     const int ni = (2 * max_R + 1 + 31) / 32;
     return 32 * (ni == 3 ? 4 : ni);

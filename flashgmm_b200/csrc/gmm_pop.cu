@@ -36,6 +36,8 @@
 // (malformed streams), rows that are not monotone (the rows kernel blanks them), the
 // bypass marker -- takes the literal path: the reference's binary search with the CDF
 // evaluated on the spot (gmm_math.cuh), uniformly in all lanes.
+#include <stdlib.h>
+
 #include "gmm_kernels.h"
 #include "gmm_math.cuh"
 
@@ -186,7 +188,13 @@ struct Ival { uint32_t lo, wd; };
 //   WIN == true : windowed record (NI == 1, 272 bytes, any R): word 0 = symbol value of lane 0's
 //                 interval, then {start, width} as two uint32 per lane for the 32 consecutive
 //                 intervals that hold the most mass -- one LDS.64 and no unpacking per symbol.
-template <int NI, bool WIN>
+// SAFE == true puts a __syncwarp() between the winner's shared-memory post and the read-back (and before the
+// group's output buffer is read): the ordering the fast variant gets from the LSU handling one warp's shared
+// accesses in program order is then guaranteed by the memory model. The fast variant is what ships; the safe
+// one (FLASHGMM_POP_SAFE=1) exists so that every toolkit bump can cross-check the two on the golden set
+// (tests/test_pop_gpu.py::test_safe_and_fast_pop_variants_agree; the SASS the ordering was verified on is
+// recorded in profiles/r02_pop_sass_fingerprint.txt).
+template <int NI, bool WIN, bool SAFE>
 __global__ void __launch_bounds__(32)
 gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode, int n_desc, int quota, int* __restrict__ claim) {
     extern __shared__ __align__(128) uint8_t ring[];
@@ -363,7 +371,9 @@ gmm_pop_rows_kernel(const PopDesc* __restrict__ descs, int mode, int n_desc, int
                     } else {
                         if (hit) asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(bc), "r"(clo), "r"(chi) : "memory");
                     }
+                    if constexpr (SAFE) __syncwarp();
                     asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(rlo), "=r"(rhi) : "r"(bc) : "memory");
+                    if constexpr (SAFE) __syncwarp();                // nobody posts the next state before everyone has read this one
                     if (hit) asm volatile("st.shared.u32 [%0], %1;" ::"r"(ob + 4u * (uint32_t)i), "r"(v) : "memory");
                     const bool need = rhi == 0u && rlo < 0x80000000u;                // rans64.h:136-141
                     xhi = need ? rlo : rhi;
@@ -443,13 +453,20 @@ cudaError_t launch_gmm_pop_rows(const PopDesc* descs_d, int n_desc, int lane_slo
     if (n_desc <= 0) return cudaSuccess;
     const size_t smem = (size_t)kPopStages * kPopStageBytes;
     const int grid = claim ? 4 * n_desc : n_desc;             // see the kernel's first lines
+    static const bool safe = [] { const char* v = getenv("FLASHGMM_POP_SAFE"); return v && *v && *v != '0'; }();
+#define FGMM_POP_LAUNCH(NI, WIN)                                                                                     \
+    do {                                                                                                             \
+        if (safe) gmm_pop_rows_kernel<NI, WIN, true><<<grid, 32, smem, st>>>(descs_d, mode, n_desc, quota, claim);   \
+        else gmm_pop_rows_kernel<NI, WIN, false><<<grid, 32, smem, st>>>(descs_d, mode, n_desc, quota, claim);       \
+    } while (0)
     switch (lane_slots) {
-    case kPopWindowed: gmm_pop_rows_kernel<1, true><<<grid, 32, smem, st>>>(descs_d, mode, n_desc, quota, claim); break;
-    case 32: gmm_pop_rows_kernel<1, false><<<grid, 32, smem, st>>>(descs_d, mode, n_desc, quota, claim); break;
-    case 64: gmm_pop_rows_kernel<2, false><<<grid, 32, smem, st>>>(descs_d, mode, n_desc, quota, claim); break;
-    case 128: gmm_pop_rows_kernel<4, false><<<grid, 32, smem, st>>>(descs_d, mode, n_desc, quota, claim); break;
+    case kPopWindowed: FGMM_POP_LAUNCH(1, true); break;
+    case 32: FGMM_POP_LAUNCH(1, false); break;
+    case 64: FGMM_POP_LAUNCH(2, false); break;
+    case 128: FGMM_POP_LAUNCH(4, false); break;
     default: return cudaErrorInvalidValue;
     }
+#undef FGMM_POP_LAUNCH
     return cudaGetLastError();
 }
 

@@ -236,3 +236,22 @@ def test_more_length_classes_than_pop_groups(pop_ctx):
         assert rc == 0 and not any(status)
         for g, wd in zip(got, want):
             assert np.array_equal(g, wd)
+
+
+def test_safe_and_fast_pop_variants_agree():
+    """the shipped pop loop relies on the LSU keeping one warp's shared-memory post and read-back
+    in program order. The __syncwarp() variant (FLASHGMM_POP_SAFE=1, read once per process) must give the same
+    symbols on the whole pop test set -- run it in a child process and let the same oracle comparisons judge it."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    if os.environ.get("FLASHGMM_POP_SAFE"):
+        pytest.skip("already the safe variant")
+    env = dict(os.environ, FLASHGMM_POP_SAFE="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", str(Path(__file__)), "-q", "-x", "-m", "gpu", "-k",
+                        "elic_shaped or every_interval or bypass_only or not_monotone or many_chunks or truncated"],
+                       env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout
