@@ -61,7 +61,7 @@ def common_config(args):
                         f"APPROX_MODE={args.mode}",
             "step": f"encode {10 * B} streams + decode {10 * B} streams ({B} images) per GPU; every step codes its images "
                     "completely, bytes identical to the reference's single-stream coder",
-            "images_per_step": B, "approx_mode": args.mode, "decode_order": args.decode_order,
+            "images_per_step": B, "approx_mode": args.mode, "decode_order": args.decode_order, "job": args.workload,
             "l2": f"inputs rotate over {N_SETS} batches of {B} images = {N_SETS * B * nsym * 52 / 1e6:.0f} MB "
                   "(one batch alone exceeds the 126 MB L2)"}
 
@@ -193,6 +193,14 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
 
     B = args.images_per_step
+    items_all = None
+    if args.workload == "sharded49":
+        # BASELINE.json configs[4] as written: 24 images + one 3840x2160 image cut into 5 x 5 tiles of 768x512 (bottom padded
+        # to 2560) = 49 independent work items of equal cost, dealt over the ranks by shard.assign: STRONG scaling
+        tiles = shard.tile_image(2160, 3840)
+        items_all = [("image", i) for i in range(24)] + [("tile", t) for t in range(len(tiles))]
+        mine = shard.my_items([1.0] * len(items_all), world, rank)
+        B = len(mine)
     sizes = elic_stream_sizes()
     n_pass = len(sizes)
     nsym = sum(sizes)
@@ -200,7 +208,10 @@ def run_b200(args):
     order = args.decode_order
     depth = max(1, args.pipeline_depth)
     # two rotating batches of B images; one batch alone (B x 25.6 MB) already exceeds L2 for B >= 5
-    batches = [[make_image(torch, synth, 1000 * rank + 100 * s + i, dev) for i in range(B)] for s in range(N_SETS)]
+    if items_all is None:
+        batches = [[make_image(torch, synth, 1000 * rank + 100 * s + i, dev) for i in range(B)] for s in range(N_SETS)]
+    else:       # the item's index seeds its content: the job codes the same 49 items whatever the number of ranks
+        batches = [[make_image(torch, synth, 50000 + 100 * s + it, dev) for it in mine] for s in range(N_SETS)]
     radii = [[[int(st[0].abs().max().item()) + 2 for st in img] for img in bt] for bt in batches]
     torch.cuda.synchronize()
     L = _lib.lib()
@@ -380,11 +391,18 @@ def run_b200(args):
 
     micro = kernel_microbench(torch, synth, L, _lib, dev, mode) if (world == 1 and not args.no_microbench) else None
 
+    item_table = None
+    if items_all is not None:
+        per_item = [(it, int(sum(streams[i * n_pass + p].size for p in range(n_pass)))) for i, it in enumerate(mine)]
+        item_table = shard.gather_item_sizes(len(items_all), per_item, device=dev)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
     total_syms = 2 * nsym * B * args.steps * world
+    item_bytes = None
+    if items_all is not None:
+        total_syms = 2 * nsym * len(items_all) * args.steps
     stream_bytes = sum(s.size for s in streams)                      # last step's bitstreams (whole batch)
     h2d = B * sum(n * 52 + n * 48 for n in sizes) + stream_bytes     # enc: symbols + params; dec: params + bitstreams
     d2h = B * sum(n * 4 + 4 + n * 4 for n in sizes) + 16 * B * len(sizes)   # enc: packed records; dec: symbols + state
@@ -421,7 +439,7 @@ def run_b200(args):
         "value": round(total_syms / secs / 1e6, 2), "unit": "Msymbols/s", "n_gpus": world,
         "steps": args.steps, "warmup": W, "ms_per_step": round(1e3 * secs / args.steps, 4),
         "ms_per_image": round(1e3 * secs / args.steps / B, 4),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "higher_is_better": True, "scaling": "weak" if items_all is None else "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": common_config(args),
         "details": {
@@ -455,10 +473,21 @@ def run_b200(args):
         "issue_peak_gwarpinst_s": round(issue_peak / 1e9, 1),
         "clocks": clocks,
     }
+    if item_table is not None:
+        line["sharded49"] = {"items": len(item_table), "items_on_rank0": B, "item_bytes": item_table,
+                             "total_bytes": int(sum(item_table)),
+                             "note": "24 images + 25 tiles (3840x2160 as 5x5 tiles of 768x512), shard.assign over the ranks; "
+                                     "per-item coded bytes gathered with shard.gather_item_sizes"}
     if micro:
         line["microbench"] = micro
+    if world == 1 and not args.no_microbench:
+        line["mode_and_radius_sweep"] = sweep_modes_and_radius(torch, synth, L, _lib, dev)
+        line["likelihood"] = likelihood_bench(torch, L, _lib, dev)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_sample(batches[0][0], radii[0][0])
+        full = reference_full_call(torch, dev)
+        if full:
+            line["cpu_baseline_full_call"] = full
     emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -547,6 +576,187 @@ def kernel_microbench(torch, synth, L, _lib, dev, mode, n=1 << 24, iters=10):
         il[f"{name}_hbm_frac"] = round(52 * n / k_ms / 1e6 / peak, 4) if k_ms > 0 else None
     res["interleaved"] = il
     return res
+
+
+def _prof_read(L, kind):
+    import ctypes as C
+    ms, n, by = C.c_double(), C.c_uint64(), C.c_double()
+    L.flashgmm_profile_read(kind, C.byref(ms), C.byref(n), C.byref(by))
+    return ms.value, n.value, by.value
+
+
+def sweep_modes_and_radius(torch, synth, L, _lib, dev, n=1 << 22, iters=5):
+    """BASELINE.json configs[2] (APPROX_MODE sweep) and VERDICT r1 #5 (cost vs search radius): the startfreq kernel
+    timed alone per mode (CUDA events on the launching stream), and one decode pass of 24 x 147 456-symbol streams
+    per mode and per search radius with the library's per-kernel event timers (rows and pop kernels)."""
+    from flashgmm_b200.batch import DecodeJob, EncodeJob
+    peak, _src = measured_peak_gbs()
+    sym, sg, mu, w = synth.gmm_torch(n, seed=4321, device=dev)
+    out = torch.empty(n, dtype=torch.int32, device=dev)
+    st = torch.cuda.Stream(device=dev)
+    h = _lib.ctx(dev.index)
+    res = {"startfreq": {}, "decode_pass": {}, "radius": {}}
+    with torch.cuda.stream(st):
+        for mode in (0, 1, 2):
+            def sf():
+                _lib.check(L.flashgmm_gmm_startfreq(h, sym.data_ptr(), sg.data_ptr(), mu.data_ptr(), w.data_ptr(), n,
+                                                    sg.stride(0), sg.stride(1), mode, out.data_ptr(), st.cuda_stream))
+            for _ in range(2):
+                sf()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            for _ in range(iters):
+                sf()
+            e1.record(st)
+            st.synchronize()
+            ms = e0.elapsed_time(e1) / iters
+            res["startfreq"][f"mode{mode}"] = {"n": n, "ms": round(ms, 4), "gsym_s": round(n / ms / 1e6, 2),
+                                               "hbm_frac": round(56 * n / ms / 1e6 / peak, 4)}
+    del out
+    streams = [synth.gmm_torch(147456, seed=900 + i, device=dev) for i in range(24)]
+    R0 = max(int(s[0].abs().max().item()) for s in streams) + 2
+
+    def decode_pass(mode, R):
+        bs = [x.copy() for x in EncodeJob(streams, mode).run()]
+        job = DecodeJob([(a, b, c, R) for (_, a, b, c) in streams], mode)
+        outs = job.run(bs)
+        assert all(torch.equal(o, s[0]) for o, s in zip(outs, streams))
+        L.flashgmm_profile_reset()
+        L.flashgmm_profile_enable(1)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            job.run(bs)
+        torch.cuda.synchronize()
+        call = (time.perf_counter() - t0) / 3
+        L.flashgmm_profile_enable(0)
+        rows_ms, rows_n, _ = _prof_read(L, 1)
+        pop_ms, pop_n, _ = _prof_read(L, 4)
+        nsym = 24 * 147456
+        return {"call_ms": round(1e3 * call, 3), "rows_kernel_ms_per_call": round(rows_ms / 3, 3),
+                "rows_gsym_s": round(nsym / (rows_ms / 3) / 1e6, 3), "call_ns_per_symbol_per_stream": round(1e9 * call / 147456, 1),
+                "decode_msym_s": round(nsym / call / 1e6, 1)}
+    for mode in (0, 1, 2):
+        res["decode_pass"][f"mode{mode}"] = decode_pass(mode, R0)
+    for R in (R0, 64, 128, 256, 1024):
+        res["radius"][f"R{R}"] = decode_pass(0, R)
+    res["note"] = ("decode_pass = one coding pass of 24 streams x 147456 symbols (device-resident); radius = the same pass "
+                   "decoded with a larger search radius than the data needs: the windowed rows kernel evaluates 33 boundaries "
+                   "per symbol whatever R is")
+    return res
+
+
+def likelihood_bench(torch, L, _lib, dev, iters=20):
+    """north_star item 5: GaussianMixtureConditional.forward (training likelihood) fwd + bwd at the training batch
+    (16 x 192 x 16 x 16, Readme.md:52) and at one ELIC image (1 x 320 x 32 x 48); algorithmic bytes 60 / 108 per element."""
+    import flashgmm_b200 as fg
+    peak, _src = measured_peak_gbs()
+    res = {}
+    for name, (B, M, H, W) in (("train_16x192x16x16", (16, 192, 16, 16)), ("elic_1x320x32x48", (1, 320, 32, 48)),
+                               ("large_64x320x32x48", (64, 320, 32, 48))):
+        g = torch.Generator(device=dev).manual_seed(7)
+        x = (torch.randn(B, M, H, W, device=dev, generator=g) * 3).requires_grad_(True)
+        sc = (torch.rand(B, 4 * M, H, W, device=dev, generator=g) * 3 + 0.05).requires_grad_(True)
+        mu = torch.randn(B, 4 * M, H, W, device=dev, generator=g).requires_grad_(True)
+        w = torch.softmax(torch.randn(B, 4, M, H, W, device=dev, generator=g), 1).reshape(B, 4 * M, H, W).requires_grad_(True)
+        m = fg.GaussianMixtureConditional(K=4).to(dev).train()
+        n = x.numel()
+        def fwd():
+            return m(x, sc, mu, w)
+        for _ in range(3):
+            y, lik = fwd()
+            lik.log().sum().backward()
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        tf, tbs = 0.0, []
+        for _ in range(iters):
+            y, lik = fwd()
+            go = torch.ones_like(lik)
+            torch.cuda.synchronize()
+            e[1].record()
+            lik.backward(go)
+            e[2].record()
+            torch.cuda.synchronize()
+            tbs.append(e[1].elapsed_time(e[2]))
+        # forward alone, back to back
+        torch.cuda.synchronize()
+        with torch.no_grad():
+            e[0].record()
+            for _ in range(iters):
+                fwd()
+            e[1].record()
+            torch.cuda.synchronize()
+            tf = e[0].elapsed_time(e[1]) / iters
+        tb = statistics.median(tbs)
+        res[name] = {"elements": n, "fwd_ms": round(tf, 4), "fwd_gb_s": round(60 * n / tf / 1e6, 1), "fwd_hbm_frac": round(60 * n / tf / 1e6 / peak, 4),
+                     "bwd_ms": round(tb, 4), "bwd_gb_s": round(108 * n / tb / 1e6, 1), "bwd_hbm_frac": round(108 * n / tb / 1e6 / peak, 4)}
+    res["note"] = ("fwd includes the noise draw (one torch kernel) and the fused likelihood kernel; bwd is the fused backward kernel "
+                   "plus autograd bookkeeping; the two small shapes are launch-latency-bound (a few microseconds of HBM time)")
+    return res
+
+
+def reference_full_call(torch, dev, repeat=3):
+    """BASELINE.md 3 'Calls timed': the reference's GaussianMixtureConditional.compress / decompress AS THE REFERENCE RUNS
+    THEM with the model on the GPU -- its tensor ops on the device, its 2 .item() + 1 .tolist() syncs and 4 D2H copies per
+    pass (entropy_models.py:833-867), its compiled CPU coder (oracle/_ref, loaded in this process), its CPU scatter and the
+    H2D of y_hat (:872-910, checkerboard.py:324) -- on one ELIC image (10 passes), parameters already on the GPU."""
+    from oracle import ref
+    if not ref.available():
+        return None
+    from flashgmm_b200 import synth
+    ans_ref = ref.load_ans()
+    enc, dec = ans_ref.RansEncoder(), ans_ref.RansDecoder()
+    K, (H, W) = 4, LATENT_HW
+    passes = []
+    for i, g in enumerate(ELIC_GROUPS):
+        for half in range(2):
+            n = g * H * W // 2
+            sym, sg, mu, w = synth.gmm_torch(n, seed=7000 + 2 * i + half, device=dev)
+            y = sym.float().reshape(1, g, H, W // 2)
+            to4 = lambda p: p.t().reshape(K, g, H, W // 2).reshape(1, K * g, H, W // 2).contiguous()  # noqa: E731
+            passes.append((y, to4(sg), to4(mu), to4(w)))
+
+    def views(t, nz):
+        return t.reshape(1, K, t.size(1) // K, -1)[:, :, nz].permute(1, 0, 2, 3).reshape(K, -1).permute(1, 0)
+
+    def compress(y, sc, mu, w):
+        abs_max = max(y.max().abs().int().item(), y.min().abs().int().item()) + 1
+        yq = torch.round(y)
+        bitmap = torch.where(torch.sum(torch.abs(yq), (3, 2)).squeeze(0) == 0, 0, 1)
+        nz = torch.nonzero(bitmap).flatten().tolist()
+        sym = yq[:, nz].reshape(-1).int()
+        b = enc.encode_with_indexes_gmm(sym.to("cpu"), views(sc, nz).clamp(0.11, 256).to("cpu"), views(mu, nz).to("cpu"),
+                                        views(w, nz).to("cpu"), abs_max + 1)
+        return b, abs_max, bitmap
+
+    def decompress(b, abs_max, bitmap, sc, mu, w):
+        nz = torch.nonzero(bitmap).flatten().tolist()
+        sym = dec.decode_with_indexes_gmm(b, views(sc, nz).clamp(0.11, 256).to("cpu"), views(mu, nz).to("cpu"),
+                                          views(w, nz).to("cpu"), abs_max + 1)
+        y_hat = torch.zeros(1, bitmap.numel(), sc.size(2), sc.size(3))
+        y_hat[:, nz] = sym.reshape(1, len(nz), sc.size(2), sc.size(3)).float()
+        return y_hat.to(dev)
+
+    nsym = sum(p[0].numel() for p in passes)
+    te = td = 0.0
+    for r in range(repeat + 1):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        coded = [compress(*p) for p in passes]
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        outs = [decompress(*c, *p[1:]) for c, p in zip(coded, passes)]
+        torch.cuda.synchronize()
+        t2 = time.perf_counter()
+        if r:
+            te += t1 - t0
+            td += t2 - t1
+    assert all(torch.equal(o, p[0]) for o, p in zip(outs, passes))
+    te /= repeat
+    td /= repeat
+    return {"value": round(2 * nsym / (te + td) / 1e6, 3), "unit": "Msymbols/s", "cores": 1, "kind": "reference",
+            "sample": f"one ELIC image (10 passes, {nsym} symbols), x{repeat}: the reference's compress/decompress call sequence "
+                      "(its torch ops on the GPU, 3 syncs + 4 D2H copies per pass, compiled CPU coder oracle/_ref, CPU scatter, H2D of y_hat)",
+            "compress_ms_per_image": round(1e3 * te, 2), "decompress_ms_per_image": round(1e3 * td, 2),
+            "encode_msym_s": round(nsym / te / 1e6, 3), "decode_msym_s": round(nsym / td / 1e6, 3)}
 
 
 # ----------------------------------------------------------------------------
@@ -685,10 +895,14 @@ def main():
     ap.add_argument("--images-per-step", type=int, default=24,
                     help="images per step and per GPU (BASELINE.json configs[4] works on 24 images)")
     ap.add_argument("--mode", type=int, default=0, choices=[0, 1, 2], help="APPROX_MODE (reference code numbering)")
+    ap.add_argument("--workload", default="images24", choices=["images24", "sharded49"],
+                    help="images24: --images-per-step images per GPU and step (weak scaling, the headline); sharded49: "
+                         "BASELINE configs[4] as written, 24 images + a 3840x2160 image as 25 tiles = 49 items dealt over "
+                         "the ranks (strong scaling)")
     ap.add_argument("--decode-order", default="pass-sequential", choices=["pass-sequential", "pass-parallel"],
                     help="pass-sequential (default, what a real decoder can do): one decode call per coding pass, "
                          "issued after the previous pass has returned; pass-parallel: every stream in one call")
-    ap.add_argument("--pipeline-depth", type=int, default=2,
+    ap.add_argument("--pipeline-depth", type=int, default=4,
                     help="independent batches in flight (host threads, one ctx each); 1 = strictly one after the other")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -342,5 +342,5 @@ struct flashgmm_ctx {
     PinBuf eb_host;                   //   ... and their page-locked landing zone / decoded symbols
     std::mutex de_mu;                 // the device encode path owns its buffers and stream: it runs beside the workers
     int push_policy = 0;              // 0 auto, 1 always host workers, 2 always device
-    double push_host_ns = 4.5, push_dev_ns = 46.0;   // per symbol: one host worker / one device warp (measured, B200 box)
+    double push_host_ns = 4.5, push_dev_ns = 46.0;   // per symbol: one host worker (calibrated at ctx creation) / one device warp (follows the push kernel's own stamps)
 };

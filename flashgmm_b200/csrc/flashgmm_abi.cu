@@ -806,6 +806,22 @@ int encode_batch_device_finish(flashgmm_ctx* ctx, flashgmm_stream* streams) {
         t_first = std::min(t_first, (unsigned long long)hr[8 * a + 4] | ((unsigned long long)hr[8 * a + 5] << 32));
         t_last = std::max(t_last, (unsigned long long)hr[8 * a + 6] | ((unsigned long long)hr[8 * a + 7] << 32));
     }
+    {
+        // the cost model's device figure follows what the push warps actually did (their own %globaltimer stamps):
+        // exponential average of ns per symbol over the streams long enough to be past start-up effects
+        double ns_sum = 0;
+        int cnt = 0;
+        for (int a = 0; a < na; ++a) {
+            const unsigned long long b = (unsigned long long)hr[8 * a + 4] | ((unsigned long long)hr[8 * a + 5] << 32);
+            const unsigned long long e = (unsigned long long)hr[8 * a + 6] | ((unsigned long long)hr[8 * a + 7] << 32);
+            const int64_t n = streams[act[a]].n;
+            if (n >= 8192 && e > b) { ns_sum += (double)(e - b) / (double)n; ++cnt; }
+        }
+        if (cnt > 0) {
+            const double seen = std::min(200.0, std::max(10.0, ns_sum / cnt));
+            ctx->push_dev_ns = 0.75 * ctx->push_dev_ns + 0.25 * seen;
+        }
+    }
     static const bool dtrace = env_long("FLASHGMM_TRACE", 0) != 0;
     if (dtrace) {
         unsigned long long latest_start = 0, longest = 0;
@@ -1223,6 +1239,31 @@ int flashgmm_ctx_create(int device, flashgmm_ctx** out) {
         c->push_policy = (pp && pp[0] == 'h') ? 1 : (pp && pp[0] == 'd') ? 2 : 0;
     }
     rcp_table();
+    if (!getenv("FLASHGMM_PUSH_HOST_NS")) {
+        // calibrate the cost model's host figure on THIS machine's cores: push 2 x 64 Ki synthetic records
+        // (~0.5 ms), keep the faster pass; x1.25 for the waves path's tail effects (measured 3.7 vs 4.5 ns)
+        std::vector<uint32_t> rec(1 << 16);
+        uint32_t lcg = 12345u;
+        for (auto& r : rec) {
+            lcg = lcg * 1664525u + 1013904223u;
+            const uint32_t freq = 1u + ((lcg >> 8) % 6000u), start = (lcg >> 20) % (65535u - freq);
+            r = start | (freq << 16);
+        }
+        double best = 1e30;
+        for (int pass = 0; pass < 2; ++pass) {
+            BackBuffer bb(rec.size());
+            RansEncoder64 enc;
+            enc.init(&bb);
+            const auto t0 = std::chrono::steady_clock::now();
+            enc.push_chunk_reverse(rec.data(), nullptr, (int64_t)rec.size());
+            enc.flush();
+            best = std::min(best, std::chrono::duration<double, std::nano>(std::chrono::steady_clock::now() - t0).count());
+        }
+        c->push_host_ns = std::min(40.0, std::max(1.5, 1.25 * best / (double)rec.size()));
+    } else {
+        c->push_host_ns = std::max(0.5, atof(getenv("FLASHGMM_PUSH_HOST_NS")));
+    }
+    if (getenv("FLASHGMM_PUSH_DEV_NS")) c->push_dev_ns = std::max(1.0, atof(getenv("FLASHGMM_PUSH_DEV_NS")));
     *out = c;
     return FLASHGMM_OK;
 }

@@ -169,3 +169,21 @@ def test_one_worker_thread(monkeypatch):
     assert rc == 0 and not any(status)
     for g, d in zip(got, data):
         assert g == port.gmm_encode(*d, 0)
+
+
+@pytest.mark.parametrize("queues", ["8", "32"])
+def test_batch_paths_with_either_hardware_queue_count(queues):
+    """the library no longer sets CUDA_DEVICE_MAX_CONNECTIONS on load. Under the reference's scripts the
+    CUDA context predates the library (8 queues, the default -- which is also what every other test here runs with);
+    bench.py asks for 32 before CUDA starts. Both configurations must give the oracle's bytes: smoke() in a child."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parents[1]
+    env = dict(os.environ, CUDA_DEVICE_MAX_CONNECTIONS=queues)
+    code = ("import torch; torch.zeros(1).cuda(); import os; assert os.environ['CUDA_DEVICE_MAX_CONNECTIONS'] == '%s'; "
+            "import __graft_entry__ as g; g.smoke()" % queues)
+    r = subprocess.run([sys.executable, "-c", code], cwd=str(root), env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "smoke ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
