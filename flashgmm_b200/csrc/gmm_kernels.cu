@@ -314,16 +314,18 @@ gmm_cdf_rows_batched_kernel(const RowsDesc* __restrict__ descs, int n_desc, int 
 // symbol of theirs takes the literal path). The window choice is therefore only a matter of speed; it uses
 // plain fast arithmetic: centre of [min_k mu_k - 3.9 sigma_k, max_k mu_k + 3.9 sigma_k] over the components
 // that carry weight (miss rate 6e-5 on the synthetic mixture of BASELINE config 4).
-constexpr int kWinThreads = 96;          // 32 symbols x 33 boundaries = 1056 = 96 x 11 points: no idle thread
+// |x - mu| <= 2^21 + 1e30 and sigma >= 2^-10 keep every quotient finite; a sane symbol whose quotient would
+// overflow does not exist for |mu| <= 1e30 (1e30 * 2^10 < FLT_MAX).
+constexpr int kWinThreads = 96;          // 32 symbols x 3 threads; a thread evaluates 11 of its symbol's 33 boundaries
 constexpr int kWinSyms = 32;
 constexpr int kWinPts = 33;
+constexpr int kWinPerThread = 11;
 
 template <int MODE>
 __global__ void __launch_bounds__(kWinThreads)
 gmm_cdf_window_batched_kernel(const RowsDesc* __restrict__ descs, int n_desc) {
-    __shared__ float prm[12][kWinSyms];                       // sg[4], mu[4], w[4]
-    __shared__ int j0s[kWinSyms];                             // first boundary index of the window, -1 = blank record
     __shared__ uint32_t T[kWinSyms][kWinPts];                 // stride 33: conflict-free both ways
+    __shared__ int j0s[kWinSyms];                             // first boundary index of the window, -1 = blank record
     int lo = 0, hi = n_desc - 1;
     const int b = (int)blockIdx.x;
     while (lo < hi) {
@@ -335,71 +337,60 @@ gmm_cdf_window_batched_kernel(const RowsDesc* __restrict__ descs, int n_desc) {
     const int live = (int)min((int64_t)kWinSyms, (int64_t)d.n - row0);
     const int R = d.R;
     const int t = (int)threadIdx.x;
+    const int sidx = t / 3, part = t - 3 * sidx;              // the symbol's 3 threads are neighbours: their loads coalesce
 
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int idx = t + kWinThreads * i;                  // 384 = 12 planes x 32 symbols
-        const int plane = idx >> 5, sidx = idx & 31;
-        float v = plane < 4 ? 1.0f : 0.0f;
-        if (sidx < live) {
-            const float* base = plane < 4 ? d.p.scales : (plane < 8 ? d.p.means : d.p.weights);
-            v = __ldg(base + (row0 + sidx) * d.p.stride_n + (plane & 3) * d.p.stride_k);
-        }
-        prm[plane][sidx] = v;
-    }
-    __syncthreads();
-    if (t < kWinSyms) {
-        float lo_x = 3.0e38f, hi_x = -3.0e38f, lo_all = 3.0e38f, hi_all = -3.0e38f;
-        bool sane = true;
-        float wsum[4];
+    // The symbol's 12 parameters stay in registers for all 11 boundaries, with the reciprocals of the scales: every
+    // boundary divides by the same four sigmas (div_by_shared_rcp, bit-identical to __fdiv_rn in the range checked below).
+    float mu[4], sg[4], w[4], rcp[4];
+    bool sane = sidx < live;
+    {
+        const int64_t i = row0 + (sane ? sidx : 0);
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const float sg = prm[k][t], mu = prm[4 + k][t], w = prm[8 + k][t];
-            sane = sane && (sg > 0.0f) && (sg <= 65536.0f) && (w >= 0.0f) && (w <= 2.0f) && (fabsf(mu) <= 1.0e30f);
-            wsum[k] = w;
-            const float a = mu - 3.9f * sg, c = mu + 3.9f * sg;
-            lo_all = fminf(lo_all, a); hi_all = fmaxf(hi_all, c);
-            if (w > 1.0e-3f) { lo_x = fminf(lo_x, a); hi_x = fmaxf(hi_x, c); }
+            const int64_t off = i * d.p.stride_n + k * d.p.stride_k;
+            sg[k] = __ldg(d.p.scales + off); mu[k] = __ldg(d.p.means + off); w[k] = __ldg(d.p.weights + off);
         }
-        // the largest value any boundary can take is the sum of the weights (same association as the CDF):
-        // it must stay below the 16-bit wrap of the quantiser
-        const float top = __fmul_rn(__fadd_rn(__fadd_rn(wsum[0], wsum[1]), __fadd_rn(wsum[2], wsum[3])), 65535.0f);
-        sane = sane && (top < 65536.0f);
-        if (hi_x < lo_x) { lo_x = lo_all; hi_x = hi_all; }
-        int j0 = -1;
-        if (sane && t < live) {
-            const float centre = fminf(fmaxf(0.5f * (lo_x + hi_x), -3.0e6f), 3.0e6f);
-            const int last = max(0, 2 * R + 1 - 32);          // last admissible first boundary
-            j0 = min(max(__float2int_rn(centre) - 16 + R, 0), last);
-        }
-        j0s[t] = j0;
     }
-    __syncthreads();
-#pragma unroll 1
-    for (int i = 0; i < 11; ++i) {
-        const int id = t + kWinThreads * i;
-        const int sidx = id / kWinPts, l = id - sidx * kWinPts;
-        const int j0 = j0s[sidx];
-        uint32_t e = 65535u;
-        if (j0 >= 0 && j0 + l <= 2 * R + 1) {
-            float mu[4], sg[4], w[4];
+    float lo_x = 3.0e38f, hi_x = -3.0e38f, lo_all = 3.0e38f, hi_all = -3.0e38f;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) { sg[k] = prm[k][sidx]; mu[k] = prm[4 + k][sidx]; w[k] = prm[8 + k][sidx]; }
-            e = gmm_q16<MODE>(__fsub_rn((float)(j0 + l - R), 0.5f), mu, sg, w);
-        }
+    for (int k = 0; k < 4; ++k) {
+        // sane: finite, scale in the range the shared-reciprocal division is checked for, weight a probability,
+        // |x - mu| small enough that neither quotient nor residual leaves the normal range
+        sane = sane && (sg[k] >= 0.0009765625f) && (sg[k] <= 65536.0f) && (w[k] >= 0.0f) && (w[k] <= 2.0f) &&
+               (fabsf(mu[k]) <= 1.0e30f);
+        rcp[k] = __frcp_rn(sg[k]);
+        const float a = mu[k] - 3.9f * sg[k], c = mu[k] + 3.9f * sg[k];
+        lo_all = fminf(lo_all, a); hi_all = fmaxf(hi_all, c);
+        if (w[k] > 1.0e-3f) { lo_x = fminf(lo_x, a); hi_x = fmaxf(hi_x, c); }
+    }
+    // the largest value any boundary can take is the sum of the weights (same association as the CDF): it must
+    // stay below the 16-bit wrap of the quantiser
+    sane = sane && (__fmul_rn(__fadd_rn(__fadd_rn(w[0], w[1]), __fadd_rn(w[2], w[3])), 65535.0f) < 65536.0f);
+    if (hi_x < lo_x) { lo_x = lo_all; hi_x = hi_all; }
+    int j0 = -1;
+    if (sane) {
+        const float centre = fminf(fmaxf(0.5f * (lo_x + hi_x), -3.0e6f), 3.0e6f);
+        j0 = min(max(__float2int_rn(centre) - 16 + R, 0), max(0, 2 * R + 1 - 32));
+    }
+    if (part == 0) j0s[sidx] = j0;
+#pragma unroll 1
+    for (int i = 0; i < kWinPerThread; ++i) {
+        const int l = part * kWinPerThread + i;
+        uint32_t e = 65535u;
+        if (j0 >= 0 && j0 + l <= 2 * R + 1) e = gmm_q16_rcp<MODE>(__fsub_rn((float)(j0 + l - R), 0.5f), mu, sg, rcp, w);
         T[sidx][l] = e;
     }
     __syncthreads();
     uint32_t* dst = d.table32 + row0 * kPopWindowWords;
     for (int id = t; id < live * kPopWindowWords; id += kWinThreads) {
-        const int sidx = id / kPopWindowWords, q = id - sidx * kPopWindowWords;
-        const int j0 = j0s[sidx];
+        const int s2 = id / kPopWindowWords, q = id - s2 * kPopWindowWords;
+        const int jj = j0s[s2];
         uint32_t v = 0;
-        if (q == 0) v = (uint32_t)((j0 < 0 ? 0 : j0) - R);
+        if (q == 0) v = (uint32_t)((jj < 0 ? 0 : jj) - R);
         else if (q >= 4) {
             const int l = (q - 4) >> 1;
-            const bool ok = j0 >= 0 && j0 + l <= 2 * R;       // interval j0 + l exists in the row
-            const uint32_t a = ok ? T[sidx][l] : 65535u, c = ok ? T[sidx][l + 1] : 65535u;
+            const bool ok = jj >= 0 && jj + l <= 2 * R;       // interval jj + l exists in the row
+            const uint32_t a = ok ? T[s2][l] : 65535u, c = ok ? T[s2][l + 1] : 65535u;
             v = (q & 1) ? c - a : a;
         }
         __stcs(dst + id, v);

@@ -47,6 +47,11 @@ __device__ __forceinline__ float exp256(float x) {
     x = fminf(x, FGMM_EXP_HI);
     x = fmaxf(x, FGMM_EXP_LO);
     float fx = __fmaf_rn(x, FGMM_LOG2EF, 0.5f);
+    // floorf + __float2int_rz are FRND + F2I on the quarter-rate XU pipe. A magic-number form on the FP32 / integer
+    // pipes (add 1.5 * 2^23, read the integer from the mantissa, one compare; exact for every finite input,
+    // tests/native/check_exact_math.c) was measured in round 2: it relieves the XU pipe (64-71 % busy in the
+    // startfreq kernel) but costs three more issue slots per exp, and these kernels are issue-bound (0.81-0.88
+    // warp-instructions per cycle and scheduler): startfreq +4 %, rows mode 2 +9 % slower. Not used.
     fx = floorf(fx);                       // floor, then "if greater subtract 1" is a no-op
     x = __fmaf_rn(-fx, FGMM_EXP_C1, x);
     x = __fmaf_rn(-fx, FGMM_EXP_C2, x);
@@ -108,6 +113,23 @@ __device__ __forceinline__ float gmm_cdf4(float x, const float (&mu)[4], const f
     return __fadd_rn(__fadd_rn(p[0], p[1]), __fadd_rn(p[2], p[3]));
 }
 
+// a / s for a divisor whose correctly rounded reciprocal y = RN(1 / s) is shared by many dividends (the 33 boundaries of
+// a symbol's window all divide by the same sigma): multiply, then two residual corrections -- after the first the
+// quotient is faithful, and Markstein's theorem makes the second correctly rounded. Five FP32-pipe operations instead
+// of MUFU.RCP + Newton steps + range check + slow-path call. Bit-identical to __fdiv_rn for 2^-10 <= s <= 2^16 and the
+// dividends this path sees (no overflow / underflow of quotient or residual): tests/native/check_exact_math.c,
+// 2 * 10^9 random pairs incl. all-ones and power-of-two significands, 0 mismatches.
+__device__ __forceinline__ float div_by_shared_rcp(float a, float s, float y) {
+    const float q0 = __fmul_rn(a, y);
+    const float q1 = __fmaf_rn(__fmaf_rn(-q0, s, a), y, q0);
+    return __fmaf_rn(__fmaf_rn(-q1, s, a), y, q1);
+}
+
+// mixture CDF with the reciprocals of the four scales precomputed (rcp[k] = __frcp_rn(sg[k]))
+template <int MODE>
+__device__ __forceinline__ uint32_t gmm_q16_rcp(float x, const float (&mu)[4], const float (&sg)[4], const float (&rcp)[4],
+                                                const float (&w)[4]);
+
 // static_cast<uint16_t>(cdf * 65535): cvttss2si then low 16 bits. x86 returns
 // 0x80000000 for NaN / |v| >= 2^31 (low half 0); __float2int_rz saturates, so
 // out-of-range is mapped to 0 explicitly.
@@ -122,6 +144,18 @@ template <int MODE>
 __device__ __forceinline__ uint32_t gmm_q16(float x, const float (&mu)[4], const float (&sg)[4],
                                             const float (&w)[4]) {
     return q16(gmm_cdf4<MODE>(x, mu, sg, w));
+}
+
+template <int MODE>
+__device__ __forceinline__ uint32_t gmm_q16_rcp(float x, const float (&mu)[4], const float (&sg)[4], const float (&rcp)[4],
+                                                const float (&w)[4]) {
+    float p[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float t = div_by_shared_rcp(__fsub_rn(x, mu[k]), sg[k], rcp[k]);
+        p[k] = __fmul_rn(w[k], phi<MODE>(t));
+    }
+    return q16(__fadd_rn(__fadd_rn(p[0], p[1]), __fadd_rn(p[2], p[3])));
 }
 
 // Packed per-symbol record handed to the host coder: start | freq << 16.

@@ -388,3 +388,20 @@ def test_container_roundtrip_and_corruption():
     for broken in (bytes(bad), blob[:-7], b"XXXX" + blob[4:], blob[:4] + b"\x09" + blob[5:]):
         with pytest.raises(container.ContainerError):
             container.unpack(broken)
+
+
+def test_exact_math_shortcuts_native_harness(tmp_path):
+    """tests/native/check_exact_math.c: (1) the magic-number floor (kept as a measured-and-rejected alternative in
+    gmm_math.cuh) equals floorf / truncation for EVERY finite binary32 input; (2) division by a shared, correctly rounded
+    reciprocal with two residual corrections (gmm_math.cuh::div_by_shared_rcp, used by the windowed rows kernel) equals
+    IEEE division on random (x - mu, sigma) pairs incl. all-ones and power-of-two significands. CPU fmaf == GPU
+    __fmaf_rn, so the result transfers. 2 * 10^8 pairs here; 2 * 10^9 were run once for DESIGN.md."""
+    import subprocess
+    from pathlib import Path
+
+    src = Path(__file__).resolve().parent / "native" / "check_exact_math.c"
+    exe = tmp_path / "chk"
+    subprocess.run(["gcc", "-O2", "-ffp-contract=off", "-mfma", "-o", str(exe), str(src), "-lm", "-lpthread"], check=True)
+    out = subprocess.run([str(exe), "200000000"], capture_output=True, text=True, timeout=600).stdout
+    assert "magic floor: 0 mismatches" in out, out
+    assert "2 corrections: 0 mismatches" in out, out
