@@ -72,7 +72,11 @@ gmm_ileave_encode_kernel(const int32_t* __restrict__ sym, GmmParamsView p, int64
             il_load(p, i, mu, sg, w);
             v = __ldg(sym + i);
             const uint32_t pk = gmm_startfreq1<MODE>(v, mu, sg, w);
-            esc = (pk == FGMM_PACK_BYPASS) || v < -R || v > R;
+            // escape also when start + freq passes 65535: only parameters that are not a probability mixture (weights
+            // summing above 1, NaN) produce that -- the 16-bit CDF wraps there, the interval would overlap the escape
+            // slot and carry into the state. For sane parameters every row is non-decreasing (oracle/check_monotone.c),
+            // which is what the decoder's search relies on; everything else travels raw.
+            esc = (pk == FGMM_PACK_BYPASS) || v < -R || v > R || ((pk & 0xffffu) + (pk >> 16) > 65535u);
             start = esc ? 65535u : (pk & 0xffffu);
             freq = esc ? 1u : (pk >> 16);
         }
