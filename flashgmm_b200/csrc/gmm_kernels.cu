@@ -341,15 +341,27 @@ gmm_cdf_window_batched_kernel(const RowsDesc* __restrict__ descs, int n_desc) {
 
     // The symbol's 12 parameters stay in registers for all 11 boundaries, with the reciprocals of the scales: every
     // boundary divides by the same four sigmas (div_by_shared_rcp, bit-identical to __fdiv_rn in the range checked below).
+    // Loaded plane by plane, 32 consecutive symbols per request (page-locked host tensors are read in place over
+    // PCIe: 128-byte requests, each parameter exactly once), handed to the symbol's threads through shared memory.
     float mu[4], sg[4], w[4], rcp[4];
     bool sane = sidx < live;
     {
-        const int64_t i = row0 + (sane ? sidx : 0);
+        float* prm = reinterpret_cast<float*>(&T[0][0]);      // 12 x 32 floats, before T is written
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int64_t off = i * d.p.stride_n + k * d.p.stride_k;
-            sg[k] = __ldg(d.p.scales + off); mu[k] = __ldg(d.p.means + off); w[k] = __ldg(d.p.weights + off);
+        for (int i = 0; i < 4; ++i) {
+            const int idx = t + kWinThreads * i;              // 384 = 12 planes x 32 symbols
+            const int plane = idx >> 5, s2 = idx & 31;
+            float v = plane < 4 ? 1.0f : 0.0f;
+            if (s2 < live) {
+                const float* base = plane < 4 ? d.p.scales : (plane < 8 ? d.p.means : d.p.weights);
+                v = __ldg(base + (row0 + s2) * d.p.stride_n + (plane & 3) * d.p.stride_k);
+            }
+            prm[idx] = v;
         }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { sg[k] = prm[32 * k + sidx]; mu[k] = prm[32 * (4 + k) + sidx]; w[k] = prm[32 * (8 + k) + sidx]; }
+        __syncthreads();                                      // T is written next
     }
     float lo_x = 3.0e38f, hi_x = -3.0e38f, lo_all = 3.0e38f, hi_all = -3.0e38f;
 #pragma unroll
