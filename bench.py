@@ -2,23 +2,32 @@
 """bench.py -- GMM rANS enc/dec throughput on B200 (BASELINE.json metric).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+                    [--decode-order pass-sequential|pass-parallel] [--pipeline-depth D]
+                    [--workload images24|sharded49] [--images-per-step B] [--mode 0|1|2]
 
-Workload (BASELINE.json configs[1]): the ten GMM streams of one ELIC2022GMM
-(M=320, groups 16/16/32/64/192, two checkerboard passes each) 768x512 image --
-491 520 symbols, K=4 -- with seeded synthetic entropy parameters (random-init
-models code ~100 % bypass). One step = encode all ten streams
-to reference-compatible single-stream rANS bytes AND decode them back.
-`value` counts every coded symbol once per direction: 2 * 491 520 per step.
+Workload (BASELINE.json configs[1] shape, batch of configs[4]): per GPU and step, the GMM streams of 24 synthetic
+768x512 ELIC2022GMM images (M=320, groups 16/16/32/64/192, two checkerboard passes each: 10 streams and 491 520
+symbols per image, K=4), seeded synthetic entropy parameters (random-init models code ~100 % bypass).
+One step = encode all 240 streams to reference-compatible single-stream rANS bytes AND decode them back, bit-exactly.
+`value` counts every coded symbol once per direction: 2 * 491 520 * 24 per step.
+
+Decode order. A real decoder gets pass p+1's parameters from pass p's decoded symbols, so the default
+is PASS-SEQUENTIAL: ten dependent decode calls per step, each carrying the 24 streams of one pass, the next one issued
+only after the previous has returned. (Round 1 decoded all 240 streams in one call; that number is kept beside the
+headline as `decode_pass_parallel_*`, labelled an upper bound.) The encoder knows all of y up front: one call.
+
+Pipeline. Images are independent, so `--pipeline-depth D` host threads (one library ctx each) each take whole steps:
+one batch's encode overlaps other batches' pass-sequential decodes on the GPU (the decode chain of a batch is serial
+and uses 24 warps; the machine has room for more). Every step still codes its own 24 images completely; K steps are
+timed from the first call to the last return. `value_one_batch_in_flight` is the D = 1 figure.
 
 Arms
-  b200      : flashgmm_b200 through its public API (C ABI underneath).
-              value = inputs resident in HBM; e2e = inputs in pinned host memory,
-              transfers inside the timed region (the kernels pull the page-locked
-              parameters over PCIe themselves; decoded symbols come back by D2H copy).
-              Encode: startfreq kernel -> host push (north_star 4). Decode: rows kernel ->
+  b200      : flashgmm_b200 through its public batch API (C ABI underneath).
+              value = inputs resident in HBM; e2e = inputs in page-locked host memory, transfers inside the timed
+              region (the kernels read the parameters over PCIe in place; bitstreams and symbols come back by copy).
+              Encode: startfreq kernels -> serial push on host workers / push kernel. Decode: windowed rows kernel ->
               pop kernel, one warp per stream, entirely on the GPU.
-  reference : the reference's own compiled CPU extension (oracle/_ref), all host
-              threads it can use (one process per stream).
+  reference : the reference's own compiled CPU extension (oracle/_ref), all host cores (one process per core).
 """
 from __future__ import annotations
 
@@ -37,11 +46,20 @@ sys.path.insert(0, str(ROOT))
 ELIC_GROUPS = (16, 16, 32, 64, 192)          # elic_gmm.py:92-93
 LATENT_HW = (32, 48)                         # 512x768 / 16
 N_SETS = 2                                   # rotating batches of images (each batch > 126 MB L2 for B >= 5)
-# (dram__bytes_read.sum + dram__bytes_write.sum) / symbols of the captured launch, from the committed
-# ncu --set full captures (profiles/r01_s22_ncu_full_*.csv: batched startfreq 786 432 symbols, rows
-# 786 432, pop 589 824, push 4.72 M); multiplied by the symbols per launch of this run to give
-# `traffic` per launch.
-NCU_DRAM_BYTES_PER_SYMBOL = {"gmm_startfreq": 52.1, "gmm_cdf_rows": 246.0, "gmm_pop_rows": 373.5, "gmm_push": 4.2}
+# Constants from the committed ncu --set full captures of round 2 (profiles/r02_ncu_summary.json, made by
+# tools/gpu_profile.sh on the same kernels: startfreq_batched 3 538 944 symbols, windowed rows 786 432, pop 786 432,
+# push 3 538 944). `traffic` in the bench line = these DRAM bytes per symbol x the symbols per launch of THIS run: it is a
+# constant from the profile, not a counter read during the run (ncu cannot run inside the timed region).
+NCU_DRAM_BYTES_PER_SYMBOL = {"gmm_startfreq": 54.9, "gmm_cdf_rows": 245.0, "gmm_pop_rows": 280.0, "gmm_push": 4.3}
+NCU_PIPES = {   # issue slots per cycle and scheduler; busiest-pipe utilisation in % of peak (sm__inst_executed_pipe_*)
+    "gmm_startfreq": {"issue_active": 0.82, "pipe_fma": 42.8, "pipe_xu": 52.2, "pipe_alu": 42.9, "source": "r02_ncu_summary.json push[0]"},
+    "gmm_cdf_rows": {"issue_active": 0.88, "pipe_fma": 45.5, "pipe_xu": 43.1, "pipe_alu": 37.7, "pipe_lsu": 25.2,
+                     "warp_insts_per_symbol": 353, "source": "r02_ncu_summary.json rows[2] (before the register-resident rewrite)"},
+    "gmm_pop_rows": {"issue_active": 0.23, "pipe_fma": 1.8, "pipe_xu": 0.0, "pipe_alu": 5.4, "warps_active_pct": 1.56,
+                     "source": "r02_ncu_summary.json pop[2]"},
+    "gmm_push": {"issue_active": 0.39, "pipe_fma": 6.0, "pipe_xu": 0.0, "pipe_alu": 9.2, "warps_active_pct": 1.56,
+                 "source": "r02_ncu_summary.json push[1]"},
+}
 ALGO_BYTES_PER_SYMBOL = {"gmm_startfreq": 56.0, "gmm_cdf_rows": 48.0 + 272.0, "gmm_pop_rows": 272.0 + 4.0, "gmm_push": 4.0 + 8.0 * 0.14}
 
 
@@ -413,8 +431,8 @@ def run_b200(args):
     notes = {
         "gmm_startfreq": "FP32-issue-bound by construction (bit-exact IEEE div/sqrt + polynomial exp, 8 Phi per symbol); "
                          "launches here are per stream and small, the 16 Mi-symbol microbench line is the kernel at size",
-        "gmm_cdf_rows": "FP32-issue-bound by construction (2R+2 = 46 CDF points x 4 components per symbol, ~10 k "
-                        "thread-instructions per symbol); DESIGN.md section 5",
+        "gmm_cdf_rows": "FP32-issue-bound by construction (33 window boundaries x 4 components per symbol whatever the search "
+                        "radius, ~47 SASS instructions per Phi); DESIGN.md section 5",
         "gmm_pop_rows": "latency-bound by construction: the rANS state recurrence is serial per stream, one warp per "
                         "stream, ~100 cycles per symbol; HBM fraction is not the figure of merit, ns/symbol/stream is",
         "gmm_push": "latency-bound by construction: the rANS state recurrence is serial per stream, one warp per "
@@ -432,6 +450,9 @@ def run_b200(args):
                 "algorithmic_bytes_per_launch": round(per_launch), "peak_source": peak_src,
                 "avg_launch_us": round(1e3 * p["ms"] / max(1, p["launches"]), 2), "launches": p["launches"],
                 "share_of_summed_kernel_time": round(p["ms"] / max(1e-9, sum(v["ms"] for v in prof.values())), 3),
+                "share_note": "share of the SUM of kernel durations (launches overlap on several CUDA streams), not of wall time",
+                "traffic_note": "DRAM bytes per symbol from profiles/r02_ncu_summary.json x symbols per launch of this run",
+                "ncu_pipes": NCU_PIPES.get(name),
                 "note": notes[name]}
 
     line = {
