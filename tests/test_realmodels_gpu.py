@@ -227,41 +227,7 @@ def test_graph_replay_equals_eager():
 
 
 # ---- plausible parameters: the synthetic mixture of config 4 in place of the random-init networks' output ----
-class SyntheticMixtures:
-    """Replaces ``_mixture`` of every GMM latent codec by a table of synthetic parameters, one entry per call in
-    coding order (the encoder and the decoder make the same calls), and draws y from them."""
-
-    def __init__(self, net, seed=1234):
-        self.codecs = [m for m in net.modules() if isinstance(m, fg.GaussianMixtureConditionalLatentCodec)]
-        self.seed = seed
-        self.calls = {}
-
-    def params(self, codec_i, call_i, B, C, H, W, K, dev):
-        g = torch.Generator().manual_seed(self.seed + 1000 * codec_i + call_i)
-        means = 3.0 * torch.randn(B, K * C, H, W, generator=g)
-        scales = 0.11 + 4.0 * torch.rand(B, K * C, H, W, generator=g)
-        weights = torch.softmax(torch.randn(B, K, C, H, W, generator=g), dim=1).reshape(B, K * C, H, W)
-        comp = torch.multinomial(weights.reshape(B, K, -1).permute(0, 2, 1).reshape(-1, K), 1, generator=g).reshape(B, 1, C, H, W)
-        pick = lambda t: torch.gather(t.reshape(B, K, C, H, W), 1, comp).squeeze(1)  # noqa: E731
-        y = pick(means) + pick(scales) * torch.randn(B, C, H, W, generator=g)
-        return scales.to(dev), means.to(dev), weights.to(dev), y.to(dev)
-
-    def __enter__(self):
-        for i, codec in enumerate(self.codecs):
-            def fake(ctx_params, codec=codec, i=i):
-                n = self.calls.get(i, 0)
-                self.calls[i] = n + 1
-                B, _, H, W = ctx_params.shape
-                C = self.channels[i]
-                sc, mu, w, _ = self.params(i, n % 2, B, C, H, W, codec.K, ctx_params.device)
-                return sc, mu, w, None
-            codec._mixture = fake
-        return self
-
-    def __exit__(self, *exc):
-        for codec in self.codecs:
-            del codec._mixture
-        return False
+from gmm_models import SyntheticMixtures  # noqa: E402
 
 
 @pytest.mark.parametrize("name", ["ckbd", "elic"])
