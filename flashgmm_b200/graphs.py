@@ -26,14 +26,17 @@ from torch import Tensor
 
 
 class _Captured:
+    """One captured instance of a step: static inputs / outputs, its graph, and the side stream it replays on."""
+
     def __init__(self, fn: Callable[..., Tuple[Tensor, ...]], example: Sequence[Tensor]):
+        dev = example[0].device
         self.inputs = [t.detach().clone() for t in example]
-        side = torch.cuda.Stream(device=example[0].device)
-        side.wait_stream(torch.cuda.current_stream(example[0].device))
-        with torch.cuda.stream(side), torch.no_grad():
+        self.stream = torch.cuda.Stream(device=dev)
+        self.stream.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(self.stream), torch.no_grad():
             for _ in range(2):                                # library warm-up outside the capture
                 fn(*self.inputs)
-        torch.cuda.current_stream(example[0].device).wait_stream(side)
+        torch.cuda.current_stream(dev).wait_stream(self.stream)
         self.graph = torch.cuda.CUDAGraph()
         with torch.no_grad(), torch.cuda.graph(self.graph):
             self.outputs = fn(*self.inputs)
@@ -55,6 +58,7 @@ class NetRunner:
             raise ValueError('net batching mode must be "per_image" or "batched"')
         self.mode = mode
         self.graphs = (os.environ.get("FLASHGMM_GRAPHS", "1") != "0") if graphs is None else bool(graphs)
+        self.lanes = max(1, int(os.environ.get("FLASHGMM_NET_LANES", "4")))   # per-image replays in flight at once
         self._cache: Dict[tuple, object] = {}
         self.replays = 0
         self.captures = 0
@@ -66,21 +70,27 @@ class NetRunner:
         if not self.graphs or not tensors[0].is_cuda or torch.is_grad_enabled() and any(t.requires_grad for t in tensors):
             with torch.no_grad():
                 return fn(*tensors)
-        sig = (key, tuple((tuple(t.shape), t.dtype, t.device) for t in tensors))
-        g = self._cache.get(sig)
-        if g is None:
-            try:
-                g = _Captured(fn, tensors)
-                self.captures += 1
-            except Exception as e:                            # capture is an optimisation of the same CUDA work
-                warnings.warn(f"flashgmm_b200: CUDA-graph capture failed ({e}); running this step eagerly")
-                g = False
-            self._cache[sig] = g
-        if g is False:
+        pool = self._instances(key, fn, tensors, 1)
+        if not pool:
             with torch.no_grad():
                 return fn(*tensors)
         self.replays += 1
-        return g(*tensors)
+        return pool[0](*tensors)
+
+    def _instances(self, key, fn, tensors, want: int):
+        """Up to `want` captured instances of the step for this input signature (each replays on its own stream)."""
+        sig = (key, tuple((tuple(t.shape), t.dtype, t.device) for t in tensors))
+        pool = self._cache.get(sig)
+        if pool is None:
+            pool = self._cache[sig] = []
+        while pool is not False and len(pool) < want:
+            try:
+                pool.append(_Captured(fn, tensors))
+                self.captures += 1
+            except Exception as e:                            # capture is an optimisation of the same CUDA work
+                warnings.warn(f"flashgmm_b200: CUDA-graph capture failed ({e}); running this step eagerly")
+                pool = self._cache[sig] = False
+        return pool
 
     def __call__(self, key, fn: Callable[..., Tuple[Tensor, ...]], *inputs: Tensor) -> Tuple[Tensor, ...]:
         inputs = tuple(t.contiguous() for t in inputs)
@@ -88,13 +98,37 @@ class NetRunner:
         if self.mode == "batched" or B == 1:
             outs = self._one(key, fn, inputs)
             return tuple(o.clone() for o in outs) if self.graphs else tuple(outs)
+        eager = (not self.graphs or not inputs[0].is_cuda
+                 or (torch.is_grad_enabled() and any(t.requires_grad for t in inputs)))
+        pool = None if eager else self._instances(key, fn, tuple(t[0:1] for t in inputs), min(self.lanes, B))
         acc = None
+        if not pool:                                          # eager, image by image
+            for b in range(B):
+                with torch.no_grad():
+                    outs = fn(*(t[b:b + 1] for t in inputs))
+                if acc is None:
+                    acc = [o.new_empty((B,) + tuple(o.shape[1:])) for o in outs]
+                for a, o in zip(acc, outs):
+                    a[b:b + 1].copy_(o)
+            return tuple(acc)
+        # image b replays on instance b % lanes: the small kernels of several images overlap on the GPU; within an
+        # instance its stream orders "copy in -> replay -> copy out" against the next image's copy in
+        cur = torch.cuda.current_stream(inputs[0].device)
+        acc = [o.new_empty((B,) + tuple(o.shape[1:])) for o in pool[0].outputs]
+        for inst in pool:
+            inst.stream.wait_stream(cur)
         for b in range(B):
-            outs = self._one(key, fn, tuple(t[b:b + 1] for t in inputs))
-            if acc is None:
-                acc = [o.new_empty((B,) + tuple(o.shape[1:])) for o in outs]
-            for a, o in zip(acc, outs):
-                a[b:b + 1].copy_(o)                           # before the next replay overwrites the graph's outputs
+            inst = pool[b % len(pool)]
+            with torch.cuda.stream(inst.stream):
+                outs = inst(*(t[b:b + 1] for t in inputs))
+                for a, o in zip(acc, outs):
+                    a[b:b + 1].copy_(o)
+            self.replays += 1
+        for inst in pool:
+            cur.wait_stream(inst.stream)
+        for t in inputs:                                      # the side streams read them: keep the allocator from reusing them early
+            for inst in pool:
+                t.record_stream(inst.stream)
         return tuple(acc)
 
 
