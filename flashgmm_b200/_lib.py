@@ -81,6 +81,7 @@ _SIGS = {
     "flashgmm_eb_compress_batch": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp,
                                              C.POINTER(Stream), _vp]),
     "flashgmm_eb_decompress_batch": (C.c_int, [_vp, C.POINTER(Stream), _i64, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp]),
+    "flashgmm_eb_likelihood": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _vp, _vp]),
     "flashgmm_scalar_gaussian_encode": (C.c_int, [_vp, _vp, _i64, C.c_int, _vp, _sz, C.POINTER(_sz)]),
     "flashgmm_scalar_gaussian_decode": (C.c_int, [_vp, _sz, _vp, _i64, C.c_int, _i32, _vp]),
     "flashgmm_rans_push_packed": (C.c_int, [_vp, _vp, _i64, _vp, _sz, C.POINTER(_sz)]),

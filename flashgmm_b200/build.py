@@ -32,6 +32,7 @@ UNITS = [
     ("gmm_prologue.cu", []),
     ("gmm_likelihood.cu", ["-Xptxas", "-v"]),
     ("gmm_table.cu", []),
+    ("eb_likelihood.cu", []),
     ("flashgmm_abi.cu", ["-Xcompiler", "-march=x86-64-v3"]),
     ("abi_glue.cu", ["-Xcompiler", "-march=x86-64-v3"]),
     ("abi_table.cu", ["-Xcompiler", "-march=x86-64-v3"]),

@@ -371,6 +371,19 @@ int flashgmm_eb_decompress_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, in
     return worst;
 }
 
+// EntropyBottleneck._likelihood, EM:434-463 (+ _logits_cumulative EM:421-440), filters (3, 3, 3, 3): device pointers,
+// asynchronous on `stream`.
+int flashgmm_eb_likelihood(flashgmm_ctx* ctx, const float* values_d, const float* params_d, int64_t C, int64_t N,
+                           float* out_d, void* stream) {
+    if (!ctx) return fail(FLASHGMM_EINVAL, "null ctx");
+    if (C < 0 || N < 0 || C > 65535) return fail(FLASHGMM_EINVAL, "bad shape C=%lld N=%lld", (long long)C, (long long)N);
+    if (C > 0 && N > 0 && (!values_d || !params_d || !out_d)) return fail(FLASHGMM_EINVAL, "null tensor");
+    CU_TRY(cudaSetDevice(ctx->device));
+    CU_TRY(launch_eb_likelihood(values_d, params_d, C, N, out_d, static_cast<cudaStream_t>(stream)));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return FLASHGMM_OK;
+}
+
 // ---- scalar single-Gaussian search coder (a14) ----
 // RansEncoder.encode_with_indexes(symbols, scales, max_value) / RansDecoder.decode_with_indexes(encoded,
 // scales, max_bs_value): RI:401-456, 600-607, 690-764 with the SCALAR approximations RI:148-150, 188-204,

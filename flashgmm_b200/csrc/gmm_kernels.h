@@ -1,6 +1,7 @@
 // gmm_kernels.h -- internal launcher interface between the C-ABI layer and the kernels.
 #pragma once
 #include <cuda_runtime.h>
+#include <algorithm>
 #include <stdint.h>
 
 namespace flashgmm {
@@ -151,5 +152,8 @@ float gmm_extremum_from_bits(uint32_t code);      // inverse of the order-preser
 cudaError_t launch_eb_records(const float* z, const float* medians, const int32_t* cdfs, const int32_t* sizes,
                               const int32_t* offsets, int64_t n_img, int C, int64_t HW, int cdf_stride,
                               unsigned long long* rec, int32_t* symbols_out, uint32_t* err, cudaStream_t st);
+
+// EntropyBottleneck._likelihood for filters (3, 3, 3, 3) (eb_likelihood.cu): values / out (C, N), params (C, 58).
+cudaError_t launch_eb_likelihood(const float* values, const float* params, int64_t C, int64_t N, float* out, cudaStream_t st);
 
 }  // namespace flashgmm

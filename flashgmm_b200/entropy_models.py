@@ -324,22 +324,38 @@ class EntropyBottleneck(_TableModel):
         return self.quantiles[:, :, 1:2]
 
     # -- density model ---------------------------------------------------------------------------
-    def _logits_cumulative(self, inputs: Tensor, stop_gradient: bool) -> Tensor:
+    def _density_parameters(self) -> List[Tensor]:
+        """[matrix0, bias0, factor0, matrix1, ..., matrix4, bias4] in layer order."""
+        depth = len(self.filters) + 1
+        out = []
+        for i in range(depth):
+            out += [getattr(self, f"_matrix{i:d}"), getattr(self, f"_bias{i:d}")]
+            if i < depth - 1:
+                out.append(getattr(self, f"_factor{i:d}"))
+        return out
+
+    def _logits_cumulative(self, inputs: Tensor, stop_gradient: bool, params: Optional[Sequence[Tensor]] = None) -> Tensor:
         """(C, 1, N) -> (C, 1, N): logits of the cumulative (entropy_models.py:421-440)."""
         logits = inputs
         depth = len(self.filters) + 1
+        it = iter(self._density_parameters() if params is None else params)
         for i in range(depth):
-            m, b = getattr(self, f"_matrix{i:d}"), getattr(self, f"_bias{i:d}")
+            m, b = next(it), next(it)
             if stop_gradient:
                 m, b = m.detach(), b.detach()
             logits = torch.matmul(F.softplus(m), logits)
             logits = logits + b
             if i < depth - 1:
-                f = getattr(self, f"_factor{i:d}")
+                f = next(it)
                 if stop_gradient:
                     f = f.detach()
                 logits = logits + torch.tanh(f) * torch.tanh(logits)
         return logits
+
+    def _likelihood_fused(self, values: Tensor) -> Tensor:
+        """Unbounded likelihood of (C, 1, N) values through csrc/eb_likelihood.cu (filters (3, 3, 3, 3), CUDA float32);
+        the backward pass recomputes the tensor-op formula under autograd."""
+        return _EBLikelihoodFn.apply(self, values, *self._density_parameters())
 
     def _likelihood(self, inputs: Tensor, stop_gradient: bool = False):
         lower = self._logits_cumulative(inputs - 0.5, stop_gradient=stop_gradient)
@@ -357,7 +373,10 @@ class EntropyBottleneck(_TableModel):
         shape = xc.size()
         values = xc.reshape(shape[0], 1, -1)
         outputs = self.quantize(values, "noise" if training else "dequantize", self._get_medians())
-        likelihood, _, _ = self._likelihood(outputs)
+        if outputs.is_cuda and outputs.dtype == torch.float32 and self.filters == (3, 3, 3, 3):
+            likelihood = self._likelihood_fused(outputs)     # one kernel instead of ~30 small tensor ops
+        else:
+            likelihood, _, _ = self._likelihood(outputs)
         if self.use_likelihood_bound:
             likelihood = self.likelihood_lower_bound(likelihood)
         outputs = outputs.reshape(shape).transpose(0, 1).contiguous()
@@ -468,6 +487,45 @@ class EntropyBottleneck(_TableModel):
             cdfs.size(1), sym.data_ptr(), _stream_of(dev)))
         med = self._get_medians().detach().reshape(1, Cc, *([1] * len(size))).to(dev)
         return self.dequantize(sym, med.expand(B, Cc, *size), med.dtype)
+
+
+class _EBLikelihoodFn(torch.autograd.Function):
+    """(module, values (C, 1, N), *density parameters) -> sigmoid(logits(v + 1/2)) - sigmoid(logits(v - 1/2))."""
+
+    @staticmethod
+    def forward(ctx, eb, values, *params):
+        C_ = values.size(0)
+        n = values.numel() // max(C_, 1)
+        packed = []
+        it = iter(params)
+        depth = len(eb.filters) + 1
+        for i in range(depth):
+            m, b = next(it), next(it)
+            packed += [F.softplus(m.detach()).reshape(C_, -1), b.detach().reshape(C_, -1)]
+            if i < depth - 1:
+                packed.append(torch.tanh(next(it).detach()).reshape(C_, -1))
+        table = torch.cat(packed, dim=1).to(torch.float32).contiguous()
+        assert table.size(1) == 58
+        v = values.detach().contiguous()
+        out = torch.empty_like(v)
+        dev = v.device
+        _lib.check(_lib.lib().flashgmm_eb_likelihood(_lib.ctx(dev.index or 0), v.data_ptr(), table.data_ptr(), C_, n,
+                                                     out.data_ptr(), _stream_of(dev)))
+        ctx.eb = eb
+        ctx.save_for_backward(values, *params)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad):
+        values, *params = ctx.saved_tensors
+        with torch.enable_grad():
+            v = values.detach().requires_grad_(True)
+            ps = [p.detach().requires_grad_(True) for p in params]
+            lower = ctx.eb._logits_cumulative(v - 0.5, False, ps)
+            upper = ctx.eb._logits_cumulative(v + 0.5, False, ps)
+            lik = torch.sigmoid(upper) - torch.sigmoid(lower)
+            grads = torch.autograd.grad(lik, [v] + ps, grad, allow_unused=True)
+        return (None, *grads)
 
 
 # --------------------------------------------------------------------------------------

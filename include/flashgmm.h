@@ -246,6 +246,14 @@ int flashgmm_eb_decompress_batch(flashgmm_ctx* ctx, flashgmm_stream* streams, in
                                  const int32_t* cdf_sizes_h, const int32_t* offsets_h, int64_t C, int64_t HW,
                                  int64_t cdf_stride, int32_t* symbols_out_d, void* stream);
 
+/* EntropyBottleneck._likelihood (EM:434-463 with _logits_cumulative EM:421-440) for filters (3, 3, 3, 3) as one kernel:
+ * values_d / out_d (C, N) float32 channel-major (what EntropyBottleneck.forward builds, EM:479-481); params_d (C, 58) =
+ * per channel softplus(matrix), bias, tanh(factor) of the five layers in order (layout: csrc/eb_likelihood.cu).
+ * out = sigmoid(logits(v + 1/2)) - sigmoid(logits(v - 1/2)); the caller applies the likelihood bound. Asynchronous on
+ * `stream`. Contract: 1e-5 relative against the reference's tensor ops. */
+int flashgmm_eb_likelihood(flashgmm_ctx* ctx, const float* values_d, const float* params_d, int64_t C, int64_t N,
+                           float* out_d, void* stream);
+
 /* ---- host-only halves (no GPU): the serial rANS recurrence ---- */
 
 /* Push packed (start|freq<<16, freq==0 = bypass -> needs symbols[i]) records:

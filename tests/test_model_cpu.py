@@ -213,3 +213,40 @@ def test_pmf_to_quantized_cdf_matches_the_reference_extension():
             p[rng.integers(0, n)] += 1.0
             p = (p / p.sum()).astype(np.float32)
             assert pmf_to_quantized_cdf(p.tolist(), 16) == list(cxx.pmf_to_quantized_cdf(p.tolist(), 16))
+
+
+def test_net_runner_eager_modes_on_cpu_tensors():
+    """graphs.NetRunner without a GPU: both batching modes run the step eagerly and agree (a 1x1 conv is batch-invariant
+    on the CPU); per-image mode assembles image b's rows from the step run on image b alone."""
+    import torch.nn as nn
+    from flashgmm_b200.graphs import NetRunner
+
+    torch.manual_seed(0)
+    conv = nn.Conv2d(6, 4, 1)
+    x = torch.randn(5, 6, 3, 7)
+    side = torch.randn(5, 2, 3, 7)
+
+    def step(a, b):
+        return (torch.cat((conv(a), b), dim=1), a.sum(dim=1, keepdim=True))
+    outs = {}
+    for mode in ("per_image", "batched"):
+        r = NetRunner(mode=mode)
+        outs[mode] = r(("k", 1), step, x, side)
+        assert r.captures == 0 and r.replays == 0               # no CUDA: nothing is captured
+        assert outs[mode][0].shape == (5, 6, 3, 7) and outs[mode][1].shape == (5, 1, 3, 7)
+    for a, b in zip(outs["per_image"], outs["batched"]):
+        torch.testing.assert_close(a, b)
+    one = NetRunner(mode="per_image")(("k", 1), step, x[2:3], side[2:3])
+    assert torch.equal(one[0], outs["per_image"][0][2:3])
+    with pytest.raises(ValueError):
+        NetRunner(mode="bogus")
+
+
+def test_mount_is_idempotent_and_keeps_own_classes():
+    import gmm_models as gm
+
+    torch.manual_seed(0)
+    net = gm.Cheng2020AnchorCheckerboardGMMv2(N=16, K=4).eval()
+    before = {id(m) for m in net.modules()}
+    assert fg.mount(net) is net and fg.mount(net) is net
+    assert {id(m) for m in net.modules()} == before          # nothing to swap in a tree built from this package's classes

@@ -320,3 +320,36 @@ def test_gradcheck_finite_differences():
             fd = float(f(*args_p) - f(*args_m)) / (2 * eps)
             an = float(leaf.grad.reshape(-1)[idx])
             assert abs(fd - an) <= 2e-3 * max(1.0, abs(an)) + 2e-4, (which, int(idx), fd, an)
+
+
+def test_entropy_bottleneck_fused_likelihood_matches_tensor_ops():
+    """csrc/eb_likelihood.cu against the module's own tensor-op formula (entropy_models.py:421-463): forward within 1e-5
+    relative (+ 1e-9), gradients equal to autograd through the tensor ops (the backward recomputes them)."""
+    torch.manual_seed(4)
+    eb = fg.EntropyBottleneck(24).cuda()
+    with torch.no_grad():
+        for p in eb.parameters():
+            p.add_(0.3 * torch.randn_like(p))
+    z = (torch.randn(3, 24, 8, 12, device="cuda") * 4).requires_grad_(True)
+    for training in (False, True):
+        torch.manual_seed(9)
+        y1, lik1 = eb(z, training=training)
+        perm = z.transpose(0, 1).contiguous().reshape(24, 1, -1)
+        torch.manual_seed(9)
+        vals = eb.quantize(perm, "noise" if training else "dequantize", eb._get_medians())
+        want, _, _ = eb._likelihood(vals)
+        want = eb.likelihood_lower_bound(want).reshape(24, 3, 8, 12).transpose(0, 1)
+        close(lik1, want.detach().cpu().numpy(), rtol=1e-5, atol=1e-9)
+        assert torch.equal(y1, vals.reshape(24, 3, 8, 12).transpose(0, 1))
+    torch.manual_seed(9)
+    _, lik = eb(z, training=True)
+    g1 = torch.autograd.grad(lik.log().sum(), [z] + list(eb.parameters()), allow_unused=True)
+    torch.manual_seed(9)
+    vals = eb.quantize(z.transpose(0, 1).contiguous().reshape(24, 1, -1), "noise", eb._get_medians())
+    want = eb.likelihood_lower_bound(eb._likelihood(vals)[0]).reshape(24, 3, 8, 12).transpose(0, 1)
+    g2 = torch.autograd.grad(want.log().sum(), [z] + list(eb.parameters()), allow_unused=True)
+    for a, b in zip(g1, g2):
+        if a is None or b is None:
+            assert a is None and b is None
+        else:
+            torch.testing.assert_close(a, b, rtol=2e-4, atol=1e-5)
