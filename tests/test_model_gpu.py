@@ -324,7 +324,9 @@ def test_gradcheck_finite_differences():
 
 def test_entropy_bottleneck_fused_likelihood_matches_tensor_ops():
     """csrc/eb_likelihood.cu against the module's own tensor-op formula (entropy_models.py:421-463): forward within 1e-5
-    relative (+ 1e-9), gradients equal to autograd through the tensor ops (the backward recomputes them)."""
+    relative + 2e-7 absolute, gradients equal to autograd through the tensor ops (the backward recomputes them).
+    The absolute term is the formula's own fp32 noise: sigmoid(upper) - sigmoid(lower) in the upper tail subtracts two
+    numbers next to 1.0, whose last bit is 6e-8 -- two correct implementations differ by that much."""
     torch.manual_seed(4)
     eb = fg.EntropyBottleneck(24).cuda()
     with torch.no_grad():
@@ -339,7 +341,7 @@ def test_entropy_bottleneck_fused_likelihood_matches_tensor_ops():
         vals = eb.quantize(perm, "noise" if training else "dequantize", eb._get_medians())
         want, _, _ = eb._likelihood(vals)
         want = eb.likelihood_lower_bound(want).reshape(24, 3, 8, 12).transpose(0, 1)
-        close(lik1, want.detach().cpu().numpy(), rtol=1e-5, atol=1e-9)
+        close(lik1, want.detach().cpu().numpy(), rtol=1e-5, atol=2e-7)
         assert torch.equal(y1, vals.reshape(24, 3, 8, 12).transpose(0, 1))
     torch.manual_seed(9)
     _, lik = eb(z, training=True)
