@@ -27,6 +27,19 @@ def info(encoded) -> dict:
     return {"n": n.value, "mode": mode.value, "R": R.value, "segment_log2": sl.value}
 
 
+_zone = None
+_zone_lock = __import__("threading").Lock()
+
+
+def _landing_zone(cap: int):
+    """Reused page-locked landing zone for the container (a fresh pageable array per call cost more than the kernel:
+    first-touch page faults + a pageable device-to-host copy; VERDICT r1 weak #12)."""
+    global _zone
+    if _zone is None or _zone.numel() < cap:
+        _zone = torch.empty(int(cap * 1.25) + 4096, dtype=torch.uint8, pin_memory=torch.cuda.is_available())
+    return _zone.numpy()[:cap]
+
+
 def encode(symbols, scales, means, weights, R: int, mode=None, segment_log2: int = 0) -> bytes:
     """Symbols outside ``[-R, R]`` (and symbols the model gives zero mass) are escaped as raw
     int32, so ``R`` trades search depth in the decoder against escapes: any ``R >= 0`` round-trips."""
@@ -45,16 +58,17 @@ def encode(symbols, scales, means, weights, R: int, mode=None, segment_log2: int
     # typical streams are ~0.5 B/symbol; retry once with the exact size if escapes blow that up
     cap = max(4096, N + (N >> 13) * 160 + 4096)
     for _ in range(2):
-        out = np.empty(cap, np.uint8)
-        n_out = C.c_size_t(0)
-        rc = L.flashgmm_gmm_ileave_encode(_lib.ctx(_dev_index(dev)), sym.data_ptr(), sc.data_ptr(), mu.data_ptr(),
-                                          w.data_ptr(), N, sn, sk, mode, mem, int(R), int(segment_log2),
-                                          out.ctypes.data, cap, C.byref(n_out))
-        if rc == _lib.ENOSPC:
-            cap = n_out.value
-            continue
-        _lib.check(rc)
-        return out[: n_out.value].tobytes()
+        with _zone_lock:
+            out = _landing_zone(cap)
+            n_out = C.c_size_t(0)
+            rc = L.flashgmm_gmm_ileave_encode(_lib.ctx(_dev_index(dev)), sym.data_ptr(), sc.data_ptr(), mu.data_ptr(),
+                                              w.data_ptr(), N, sn, sk, mode, mem, int(R), int(segment_log2),
+                                              out.ctypes.data, cap, C.byref(n_out))
+            if rc == _lib.ENOSPC:
+                cap = n_out.value
+                continue
+            _lib.check(rc)
+            return out[: n_out.value].tobytes()
     raise RuntimeError("unreachable")
 
 
