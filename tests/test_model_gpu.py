@@ -343,15 +343,18 @@ def test_entropy_bottleneck_fused_likelihood_matches_tensor_ops():
         want = eb.likelihood_lower_bound(want).reshape(24, 3, 8, 12).transpose(0, 1)
         close(lik1, want.detach().cpu().numpy(), rtol=1e-5, atol=2e-7)
         assert torch.equal(y1, vals.reshape(24, 3, 8, 12).transpose(0, 1))
-    torch.manual_seed(9)
-    _, lik = eb(z, training=True)
-    g1 = torch.autograd.grad(lik.log().sum(), [z] + list(eb.parameters()), allow_unused=True)
-    torch.manual_seed(9)
-    vals = eb.quantize(z.transpose(0, 1).contiguous().reshape(24, 1, -1), "noise", eb._get_medians())
-    want = eb.likelihood_lower_bound(eb._likelihood(vals)[0]).reshape(24, 3, 8, 12).transpose(0, 1)
-    g2 = torch.autograd.grad(want.log().sum(), [z] + list(eb.parameters()), allow_unused=True)
-    for a, b in zip(g1, g2):
-        if a is None or b is None:
-            assert a is None and b is None
-        else:
-            torch.testing.assert_close(a, b, rtol=2e-4, atol=1e-5)
+    # gradients: the backward recomputes the tensor-op formula, so d(sum lik) agrees tightly; d(sum log lik) also carries
+    # 1 / lik of the fused forward, which amplifies the formula's absolute noise on tail values (lik ~ 1e-6)
+    for reduce, rtol, atol in ((lambda t: t.sum(), 1e-5, 1e-6), (lambda t: t.log().sum(), 5e-3, 1e-3)):
+        torch.manual_seed(9)
+        _, lik = eb(z, training=True)
+        g1 = torch.autograd.grad(reduce(lik), [z] + list(eb.parameters()), allow_unused=True)
+        torch.manual_seed(9)
+        vals = eb.quantize(z.transpose(0, 1).contiguous().reshape(24, 1, -1), "noise", eb._get_medians())
+        want = eb.likelihood_lower_bound(eb._likelihood(vals)[0]).reshape(24, 3, 8, 12).transpose(0, 1)
+        g2 = torch.autograd.grad(reduce(want), [z] + list(eb.parameters()), allow_unused=True)
+        for a, b in zip(g1, g2):
+            if a is None or b is None:
+                assert a is None and b is None
+            else:
+                torch.testing.assert_close(a, b, rtol=rtol, atol=atol)

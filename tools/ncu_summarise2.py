@@ -20,8 +20,10 @@ KEYS = {
     "smsp__average_warp_latency_per_inst_issued.ratio": "warp_latency_per_inst",
 }
 out = {}
-for name in ("sf", "rows", "pop", "push", "lik", "il", "glue"):
-    rep = f"{O}/r02_{name}.ncu-rep"
+for name in ("sf", "rows", "pop", "push", "lik", "il", "glue", "rows_final", "lik_final"):
+    # *_final: recaptured after the register-resident rewrite of the windowed rows kernel (all three modes) and with the
+    # EntropyBottleneck likelihood kernel (tools/gpu_final.sh writes them as r02b_*)
+    rep = f"{O}/r02b_{name[:-6]}.ncu-rep" if name.endswith("_final") else f"{O}/r02_{name}.ncu-rep"
     if not os.path.exists(rep):
         continue
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
