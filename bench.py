@@ -53,8 +53,9 @@ N_SETS = 2                                   # rotating batches of images (each 
 NCU_DRAM_BYTES_PER_SYMBOL = {"gmm_startfreq": 54.9, "gmm_cdf_rows": 245.0, "gmm_pop_rows": 280.0, "gmm_push": 4.3}
 NCU_PIPES = {   # issue slots per cycle and scheduler; busiest-pipe utilisation in % of peak (sm__inst_executed_pipe_*)
     "gmm_startfreq": {"issue_active": 0.82, "pipe_fma": 42.8, "pipe_xu": 52.2, "pipe_alu": 42.9, "source": "r02_ncu_summary.json push[0]"},
-    "gmm_cdf_rows": {"issue_active": 0.88, "pipe_fma": 45.5, "pipe_xu": 43.1, "pipe_alu": 37.7, "pipe_lsu": 25.2,
-                     "warp_insts_per_symbol": 353, "source": "r02_ncu_summary.json rows[2] (before the register-resident rewrite)"},
+    "gmm_cdf_rows": {"issue_active": 0.87, "pipe_fma": 49.0, "pipe_xu": 30.5, "pipe_alu": 44.6, "pipe_lsu": 14.1,
+                     "warp_insts_per_symbol": 316, "by_mode_us_per_786432_symbols": {"0": 262, "1": 293, "2": 325},
+                     "source": "r02_ncu_summary.json rows_final (after the register-resident rewrite)"},
     "gmm_pop_rows": {"issue_active": 0.23, "pipe_fma": 1.8, "pipe_xu": 0.0, "pipe_alu": 5.4, "warps_active_pct": 1.56,
                      "source": "r02_ncu_summary.json pop[2]"},
     "gmm_push": {"issue_active": 0.39, "pipe_fma": 6.0, "pipe_xu": 0.0, "pipe_alu": 9.2, "warps_active_pct": 1.56,
