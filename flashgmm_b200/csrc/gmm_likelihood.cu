@@ -15,6 +15,8 @@
 // (entropy_models.py:784-787), i.e. K planes of M*HW floats per batch item.
 // Numerics follow the reference's operation order in fp32 with the exact erfcf
 // (contract: 1e-5 relative; not a bit-exact path).
+#include <stdlib.h>
+
 #include "gmm_kernels.h"
 
 namespace flashgmm {
@@ -113,6 +115,20 @@ gmm_likelihood_fwd_kernel(const float* __restrict__ x, const float* __restrict__
     }
 }
 
+// VEC consecutive floats with one streaming load / store (VEC = 1, 2 or 4; 4 * VEC-byte aligned)
+template <int VEC>
+__device__ __forceinline__ void ldv(const float* p, float (&v)[VEC]) {
+    if constexpr (VEC == 4) { const float4 t = __ldcs(reinterpret_cast<const float4*>(p)); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
+    else if constexpr (VEC == 2) { const float2 t = __ldcs(reinterpret_cast<const float2*>(p)); v[0] = t.x; v[1] = t.y; }
+    else v[0] = *p;
+}
+template <int VEC>
+__device__ __forceinline__ void stv(float* p, const float (&v)[VEC]) {
+    if constexpr (VEC == 4) __stcs(reinterpret_cast<float4*>(p), make_float4(v[0], v[1], v[2], v[3]));
+    else if constexpr (VEC == 2) __stcs(reinterpret_cast<float2*>(p), make_float2(v[0], v[1]));
+    else *p = v[0];
+}
+
 // Backward. Given g = dL/d(likelihood after the bound):
 //   g' = g if (lik_raw >= bound) or (g < 0) else 0                         (bound_ops.py:40-42)
 //   l_k = Phi(u) - Phi(d), u = (0.5 - v)/s, d = (-0.5 - v)/s, v = |y - mu_k|, s = max(sigma_k, sb)
@@ -132,15 +148,8 @@ gmm_likelihood_bwd_kernel(const float* __restrict__ y, const float* __restrict__
         const int64_t b = e / g.plane, i = e - b * g.plane;
         const int64_t pidx = b * g.plane * g.K + i;
         float yv[VEC], gv[VEC];
-        if (VEC == 4) {
-            float4 t = __ldcs(reinterpret_cast<const float4*>(y + e));
-            float4 q = __ldcs(reinterpret_cast<const float4*>(grad + e));
-            yv[0] = t.x; yv[1] = t.y; yv[2] = t.z; yv[3] = t.w;
-            gv[0] = q.x; gv[1] = q.y; gv[2] = q.z; gv[3] = q.w;
-        } else {
-            yv[0] = y[e];
-            gv[0] = grad[e];
-        }
+        ldv<VEC>(y + e, yv);
+        ldv<VEC>(grad + e, gv);
         constexpr int KA = KT ? KT : kMaxK;
         const int K = KT ? KT : g.K;
         float lk[KA][VEC], dv[KA][VEC], ds[KA][VEC], wk[KA][VEC], sraw[KA][VEC];
@@ -151,16 +160,9 @@ gmm_likelihood_bwd_kernel(const float* __restrict__ y, const float* __restrict__
         for (int k = 0; k < KA; ++k) {
             if (k < K) {
                 float ss[VEC], mm[VEC], ww[VEC];
-                if (VEC == 4) {
-                    const float4 s4 = __ldcs(reinterpret_cast<const float4*>(sc + pidx + k * g.plane));
-                    const float4 m4 = __ldcs(reinterpret_cast<const float4*>(mu + pidx + k * g.plane));
-                    const float4 w4 = __ldcs(reinterpret_cast<const float4*>(w + pidx + k * g.plane));
-                    ss[0] = s4.x; ss[1] = s4.y; ss[2] = s4.z; ss[3] = s4.w;
-                    mm[0] = m4.x; mm[1] = m4.y; mm[2] = m4.z; mm[3] = m4.w;
-                    ww[0] = w4.x; ww[1] = w4.y; ww[2] = w4.z; ww[3] = w4.w;
-                } else {
-                    ss[0] = sc[pidx + k * g.plane]; mm[0] = mu[pidx + k * g.plane]; ww[0] = w[pidx + k * g.plane];
-                }
+                ldv<VEC>(sc + pidx + k * g.plane, ss);
+                ldv<VEC>(mu + pidx + k * g.plane, mm);
+                ldv<VEC>(w + pidx + k * g.plane, ww);
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) {
                     const float s = fmaxf(ss[j], scale_bound);
@@ -199,17 +201,12 @@ gmm_likelihood_bwd_kernel(const float* __restrict__ y, const float* __restrict__
                     a[j] = gs; bq[j] = -gyk; c[j] = gv[j] * lk[k][j];
                 }
                 const int64_t o = pidx + k * g.plane;
-                if (VEC == 4) {
-                    __stcs(reinterpret_cast<float4*>(gsc + o), make_float4(a[0], a[1], a[2], a[3]));
-                    __stcs(reinterpret_cast<float4*>(gmu + o), make_float4(bq[0], bq[1], bq[2], bq[3]));
-                    __stcs(reinterpret_cast<float4*>(gw + o), make_float4(c[0], c[1], c[2], c[3]));
-                } else {
-                    gsc[o] = a[0]; gmu[o] = bq[0]; gw[o] = c[0];
-                }
+                stv<VEC>(gsc + o, a);
+                stv<VEC>(gmu + o, bq);
+                stv<VEC>(gw + o, c);
             }
         }
-        if (VEC == 4) __stcs(reinterpret_cast<float4*>(gy + e), make_float4(gyv[0], gyv[1], gyv[2], gyv[3]));
-        else gy[e] = gyv[0];
+        stv<VEC>(gy + e, gyv);
     }
 }
 
@@ -248,8 +245,14 @@ cudaError_t launch_gmm_likelihood_bwd(const float* y, const float* sc, const flo
     if (g.total <= 0) return cudaSuccess;
     const bool vec = (plane % 4 == 0) && al16(y) && al16(sc) && al16(mu) && al16(w) && al16(grad) && al16(gy) &&
                      al16(gsc) && al16(gmu) && al16(gw);
-    if (vec && K == 4)
+    // two elements per thread: the per-element state of the second pass (5 x K values) is what limits occupancy --
+    // 116 registers and 23 % warps active with four elements (ncu r02), FLASHGMM_LK_BWD_VEC=4 brings that form back
+    static const int bwd_vec = [] { const char* v = getenv("FLASHGMM_LK_BWD_VEC"); return v && *v == '4' ? 4 : 2; }();
+    if (vec && K == 4 && bwd_vec == 4)
         gmm_likelihood_bwd_kernel<4, 4><<<lk_grid(g.total / 4), kLkThreads, 0, st>>>(y, sc, mu, w, grad, g, scale_bound,
+                                                                                   lik_bound, gy, gsc, gmu, gw);
+    else if (vec && K == 4)
+        gmm_likelihood_bwd_kernel<2, 4><<<lk_grid(g.total / 2), kLkThreads, 0, st>>>(y, sc, mu, w, grad, g, scale_bound,
                                                                                    lik_bound, gy, gsc, gmu, gw);
     else if (K == 4)
         gmm_likelihood_bwd_kernel<1, 4><<<lk_grid(g.total), kLkThreads, 0, st>>>(y, sc, mu, w, grad, g, scale_bound,
