@@ -232,9 +232,8 @@ def run_b200(args):
     mode = args.mode
     order = args.decode_order
     depth = args.pipeline_depth
-    if depth <= 0:      # auto: 6 batches in flight with >= 12 host cores per rank (measured 2818 vs 2282 Msym/s at 4), else 4
-        per_rank_cores = (os.cpu_count() or 1) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", str(world))))
-        depth = 6 if per_rank_cores >= 12 else 4
+    if depth <= 0:      # default: 6 batches in flight. Measured (Msym/s, depth 4 -> 6): N=1 2282 -> 2818, N=4 7867 -> 10384,
+        depth = 6       # N=8 15810 -> 17253; 8 adds 2 % at N=1
     # two rotating batches of B images; one batch alone (B x 25.6 MB) already exceeds L2 for B >= 5
     if items_all is None:
         batches = [[make_image(torch, synth, 1000 * rank + 100 * s + i, dev) for i in range(B)] for s in range(N_SETS)]
@@ -1015,7 +1014,7 @@ def main():
                          "issued after the previous pass has returned; pass-parallel: every stream in one call")
     ap.add_argument("--pipeline-depth", type=int, default=0,
                     help="independent batches in flight (host threads, one ctx each); 1 = strictly one after the other; "
-                         "0 (default) = 6 with >= 12 host cores per rank, else 4")
+                         "0 (default) = 6")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
