@@ -676,6 +676,12 @@ def sweep_modes_and_radius(torch, synth, L, _lib, dev, n=1 << 22, iters=5):
         res["decode_pass"][f"mode{mode}"] = decode_pass(mode, R0)
     for R in (R0, 64, 128, 256, 1024):
         res["radius"][f"R{R}"] = decode_pass(0, R)
+    # peaky mixtures (sigma in [0.11, 0.9], close means: what trained latents look like): most window boundaries are
+    # saturated and the rows kernel skips their evaluation exactly
+    broad = streams
+    streams = [synth.gmm_torch(147456, seed=950 + i, device=dev, sigma_span=0.8, mean_scale=1.0) for i in range(24)]
+    res["peaky"] = {f"mode{m}": decode_pass(m, max(int(s[0].abs().max().item()) for s in streams) + 2) for m in (0, 1, 2)}
+    streams = broad
     res["note"] = ("decode_pass = one coding pass of 24 streams x 147456 symbols (device-resident); radius = the same pass "
                    "decoded with a larger search radius than the data needs: the windowed rows kernel evaluates 33 boundaries "
                    "per symbol whatever R is")

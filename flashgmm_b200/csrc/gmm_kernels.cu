@@ -385,11 +385,36 @@ gmm_cdf_window_batched_kernel(const RowsDesc* __restrict__ descs, int n_desc) {
         j0 = min(max(__float2int_rn(centre) - 16 + R, 0), max(0, 2 * R + 1 - 32));
     }
     if (part == 0) j0s[sidx] = j0;
+    // Saturated boundaries are not evaluated. Each Phi approximation reaches EXACTLY 1.0f at t >= kSatHi and (modes 0, 1)
+    // exactly +0.0f at t <= -kSatLo (thresholds found by bisection over the bit patterns with the CPU restatement; Phi is
+    // monotone over every finite argument, oracle/check_monotone.c, so it stays there). Beyond x_hi every component is at
+    // 1.0: the boundary is q16((w0 + w1) + (w2 + w3)); below x_lo every component is at +0: the boundary is 0 -- the very
+    // values the full evaluation produces. The 0.05 on the thresholds and the slack of half a symbol plus 2^-18 relative
+    // cover the rounding of this float arithmetic. Real latents have small sigmas: most of a 33-boundary window is
+    // saturated (the window is centred on the active span, so the same iterations are skipped by all lanes of a warp).
+    constexpr float kSatHi = (MODE == MODE_POLYA ? 4.9690776f : MODE == MODE_AS ? 5.4203959f : 9.7741079f) + 0.05f;
+    constexpr float kSatLo = (MODE == MODE_POLYA ? 5.2172627f : 5.4203959f) + 0.05f;
+    float x_lo = 3.0e38f, x_hi = -3.0e38f;
+    bool skip_ok = true;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        skip_ok = skip_ok && fabsf(mu[k]) <= 2097152.0f;
+        x_lo = fminf(x_lo, mu[k] - kSatLo * sg[k]);
+        x_hi = fmaxf(x_hi, mu[k] + kSatHi * sg[k]);
+    }
+    x_lo = (skip_ok && MODE != MODE_LOGISTIC) ? x_lo - 0.5f - fabsf(x_lo) * 3.8147e-6f : -3.0e38f;
+    x_hi = skip_ok ? x_hi + 0.5f + fabsf(x_hi) * 3.8147e-6f : 3.0e38f;
+    const uint32_t top = q16(__fadd_rn(__fadd_rn(w[0], w[1]), __fadd_rn(w[2], w[3])));
 #pragma unroll 1
     for (int i = 0; i < kWinPerThread; ++i) {
-        const int l = part * kWinPerThread + i;
+        const int l = part + 3 * i;                           // interleaved: the symbol's active boundaries are shared out evenly
         uint32_t e = 65535u;
-        if (j0 >= 0 && j0 + l <= 2 * R + 1) e = gmm_q16_rcp<MODE>(__fsub_rn((float)(j0 + l - R), 0.5f), mu, sg, rcp, w);
+        if (j0 >= 0 && j0 + l <= 2 * R + 1) {
+            const float x = __fsub_rn((float)(j0 + l - R), 0.5f);
+            if (x >= x_hi) e = top;
+            else if (x <= x_lo) e = 0u;
+            else e = gmm_q16_rcp<MODE>(x, mu, sg, rcp, w);
+        }
         T[sidx][l] = e;
     }
     __syncthreads();

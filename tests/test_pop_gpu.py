@@ -255,3 +255,28 @@ def test_safe_and_fast_pop_variants_agree():
                        env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert " passed" in r.stdout
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_peaky_mixtures_with_saturated_boundaries(pop_ctx, mode):
+    """Small sigmas (what trained latents look like): most of the 33 window boundaries are saturated and the rows kernel
+    takes them from the closed form (0 below, q16(sum of weights) above) instead of evaluating Phi. Valid AND garbage
+    streams (garbage makes cum land in every interval, saturated ones included), large search radius, components both
+    clustered and far apart, and scales right at the 0.11 clamp."""
+    rng = np.random.default_rng(50 + mode)
+    items, want = [], []
+    for i, (span, mscale, R) in enumerate([(0.4, 0.7, 40), (1.2, 2.0, 200), (0.0, 6.0, 90), (2.5, 0.2, 1000)]):
+        n = 6000 + 11 * i
+        sym, sg, mu, w = synth.gmm_numpy(n, seed=900 + 10 * mode + i, sigma_span=span, mean_scale=mscale)
+        sym = np.clip(sym, -(R - 1), R - 1).astype(np.int32)
+        for garbage in (False, True):
+            b = (rng.integers(0, 256, 4 * (12 * n + 16), dtype=np.uint8).tobytes() if garbage
+                 else port.gmm_encode(sym, sg, mu, w, mode))
+            items.append((b, sg, mu, w, R))
+            want.append(port.gmm_decode(b, sg, mu, w, R, mode))
+            if not garbage:
+                assert np.array_equal(want[-1], sym)
+    got, status, rc = decode_batch(pop_ctx(), items, mode)
+    assert rc == 0 and not any(status)
+    for g, wd in zip(got, want):
+        assert np.array_equal(g, wd)
