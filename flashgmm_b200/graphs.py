@@ -26,24 +26,35 @@ from torch import Tensor
 
 
 class _Captured:
-    """One captured instance of a step: static inputs / outputs, its graph, and the side stream it replays on."""
+    """One captured instance of a step: static inputs / outputs for `group` images, its graph, and the side stream it
+    replays on. With group > 1 the graph contains the step `group` times, each on ONE image (batch-1 shapes, so every
+    image gets exactly the kernels and summation orders of coding it alone) -- one replay then serves several images."""
 
-    def __init__(self, fn: Callable[..., Tuple[Tensor, ...]], example: Sequence[Tensor]):
+    def __init__(self, fn: Callable[..., Tuple[Tensor, ...]], example: Sequence[Tensor], group: int = 0):
         dev = example[0].device
+        self.group = group
         self.inputs = [t.detach().clone() for t in example]
         self.stream = torch.cuda.Stream(device=dev)
+
+        def run():
+            if group <= 0:
+                return fn(*self.inputs)
+            per = [fn(*(t[g:g + 1] for t in self.inputs)) for g in range(group)]
+            return tuple(torch.cat([o[j] for o in per], dim=0) for j in range(len(per[0])))
+
         self.stream.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(self.stream), torch.no_grad():
             for _ in range(2):                                # library warm-up outside the capture
-                fn(*self.inputs)
+                run()
         torch.cuda.current_stream(dev).wait_stream(self.stream)
         self.graph = torch.cuda.CUDAGraph()
         with torch.no_grad(), torch.cuda.graph(self.graph):
-            self.outputs = fn(*self.inputs)
+            self.outputs = run()
 
     def __call__(self, *tensors: Tensor) -> Tuple[Tensor, ...]:
+        n = tensors[0].size(0)
         for dst, src in zip(self.inputs, tensors):
-            dst.copy_(src)
+            dst[:n].copy_(src)
         self.graph.replay()
         return self.outputs
 
@@ -77,15 +88,15 @@ class NetRunner:
         self.replays += 1
         return pool[0](*tensors)
 
-    def _instances(self, key, fn, tensors, want: int):
+    def _instances(self, key, fn, tensors, want: int, group: int = 0):
         """Up to `want` captured instances of the step for this input signature (each replays on its own stream)."""
-        sig = (key, tuple((tuple(t.shape), t.dtype, t.device) for t in tensors))
+        sig = (key, group, tuple((tuple(t.shape), t.dtype, t.device) for t in tensors))
         pool = self._cache.get(sig)
         if pool is None:
             pool = self._cache[sig] = []
         while pool is not False and len(pool) < want:
             try:
-                pool.append(_Captured(fn, tensors))
+                pool.append(_Captured(fn, tensors, group))
                 self.captures += 1
             except Exception as e:                            # capture is an optimisation of the same CUDA work
                 warnings.warn(f"flashgmm_b200: CUDA-graph capture failed ({e}); running this step eagerly")
@@ -100,7 +111,9 @@ class NetRunner:
             return tuple(o.clone() for o in outs) if self.graphs else tuple(outs)
         eager = (not self.graphs or not inputs[0].is_cuda
                  or (torch.is_grad_enabled() and any(t.requires_grad for t in inputs)))
-        pool = None if eager else self._instances(key, fn, tuple(t[0:1] for t in inputs), min(self.lanes, B))
+        group = -(-B // self.lanes)                           # images per replay
+        n_inst = -(-B // group)
+        pool = None if eager else self._instances(key, fn, tuple(t[0:group] for t in inputs), n_inst, group)
         acc = None
         if not pool:                                          # eager, image by image
             for b in range(B):
@@ -111,23 +124,21 @@ class NetRunner:
                 for a, o in zip(acc, outs):
                     a[b:b + 1].copy_(o)
             return tuple(acc)
-        # image b replays on instance b % lanes: the small kernels of several images overlap on the GPU; within an
-        # instance its stream orders "copy in -> replay -> copy out" against the next image's copy in
+        # images [i * group, (i + 1) * group) replay on instance i: the small kernels of several images overlap on the
+        # GPU, and one replay (one launch from Python) serves `group` images
         cur = torch.cuda.current_stream(inputs[0].device)
         acc = [o.new_empty((B,) + tuple(o.shape[1:])) for o in pool[0].outputs]
-        for inst in pool:
+        for i, inst in enumerate(pool[:n_inst]):
+            b0, b1 = i * group, min(B, (i + 1) * group)
             inst.stream.wait_stream(cur)
-        for b in range(B):
-            inst = pool[b % len(pool)]
             with torch.cuda.stream(inst.stream):
-                outs = inst(*(t[b:b + 1] for t in inputs))
+                outs = inst(*(t[b0:b1] for t in inputs))
                 for a, o in zip(acc, outs):
-                    a[b:b + 1].copy_(o)
+                    a[b0:b1].copy_(o[: b1 - b0])
             self.replays += 1
-        for inst in pool:
+        for inst in pool[:n_inst]:
             cur.wait_stream(inst.stream)
-        for t in inputs:                                      # the side streams read them: keep the allocator from reusing them early
-            for inst in pool:
+            for t in list(inputs) + acc:                      # the side streams touch them: keep the allocator from reusing them early
                 t.record_stream(inst.stream)
         return tuple(acc)
 
