@@ -76,7 +76,12 @@ gmm_ileave_encode_kernel(const int32_t* __restrict__ sym, GmmParamsView p, int64
             // summing above 1, NaN) produce that -- the 16-bit CDF wraps there, the interval would overlap the escape
             // slot and carry into the state. For sane parameters every row is non-decreasing (oracle/check_monotone.c),
             // which is what the decoder's search relies on; everything else travels raw.
-            esc = (pk == FGMM_PACK_BYPASS) || v < -R || v > R || ((pk & 0xffffu) + (pk >> 16) > 65535u);
+            // ... and when the parameters are not a sane mixture at all (a scale that is not positive and finite, a negative
+            // or NaN weight): only sane parameters guarantee the non-decreasing row the decoder's search assumes
+            bool sane = true;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) sane = sane && (sg[k] > 0.0f) && (sg[k] <= 3.0e38f) && (w[k] >= 0.0f) && (fabsf(mu[k]) <= 3.0e38f);
+            esc = (pk == FGMM_PACK_BYPASS) || v < -R || v > R || ((pk & 0xffffu) + (pk >> 16) > 65535u) || !sane;
             start = esc ? 65535u : (pk & 0xffffu);
             freq = esc ? 1u : (pk >> 16);
         }

@@ -125,3 +125,22 @@ def test_corrupt_containers_are_rejected():
     bad = bytearray(blob); bad[32 + 4] ^= 0x10                            # segment boundary moved: caught by the kernel
     with pytest.raises(Exception):
         ileave.decode(bytes(bad), a, m, ww)
+
+
+def test_parameters_that_are_not_a_mixture_still_roundtrip():
+    """weights summing above 1 wrap the 16-bit CDF (start + freq > 65535 would overlap the escape slot), negative or
+    NaN weights / scales break the row's monotonicity the decoder's search relies on. Such symbols are escaped (raw int32):
+    the container round-trips whatever the parameters are, and the GPU still writes the CPU statement's bytes."""
+    sym, sg, mu, w = case(20_000, 21, outliers=False)
+    sg, mu, w = (np.ascontiguousarray(x).copy() for x in (sg, mu, w))
+    w[100:4000] *= 3.0                     # unnormalised: sums to 3
+    w[5000:5200, 1] = -0.25                # negative weight
+    w[6000:6050, 2] = np.nan
+    sg[7000:7100, 0] = 0.0
+    sg[7200:7300, 3] = -1.0
+    mu[8000:8050, 1] = np.inf
+    s, a, m, ww = dev(sym, sg, mu, w)
+    for mode in (0, 1, 2):
+        blob = ileave.encode(s, a, m, ww, 30, mode, 11)
+        assert blob == port.ileave_encode(sym, sg, mu, w, 30, mode, 11)
+        assert torch.equal(ileave.decode(blob, a, m, ww), s)
