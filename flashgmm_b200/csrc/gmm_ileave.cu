@@ -81,6 +81,7 @@ gmm_ileave_encode_kernel(const int32_t* __restrict__ sym, GmmParamsView p, int64
             bool sane = true;
 #pragma unroll
             for (int k = 0; k < 4; ++k) sane = sane && (sg[k] > 0.0f) && (sg[k] <= 3.0e38f) && (w[k] >= 0.0f) && (fabsf(mu[k]) <= 3.0e38f);
+            sane = sane && (__fmul_rn(__fadd_rn(__fadd_rn(w[0], w[1]), __fadd_rn(w[2], w[3])), 65535.0f) < 65536.0f);   // no 16-bit wrap anywhere in the row
             esc = (pk == FGMM_PACK_BYPASS) || v < -R || v > R || ((pk & 0xffffu) + (pk >> 16) > 65535u) || !sane;
             start = esc ? 65535u : (pk & 0xffffu);
             freq = esc ? 1u : (pk >> 16);
