@@ -110,10 +110,11 @@ int flashgmm_gmm_decode(flashgmm_ctx* ctx, const uint8_t* encoded, size_t encode
 /* Many independent streams in one call (one per checkerboard pass / channel group /
  * image). The rANS recurrence is serial within a stream, so the stream is the unit of
  * parallelism:
- *   decode: batches of >= 4 streams (FLASHGMM_POP_MIN_STREAMS) with max_bs_value <= 1023 never
- *           leave the GPU -- a batched rows kernel writes per-symbol interval records, a pop
- *           kernel walks each stream's state with one warp (gmm_pop.cu); smaller batches and
- *           larger radii run the rows kernel per stream and pop on the ctx's worker threads;
+ *   decode: batches of >= 4 streams (FLASHGMM_POP_MIN_STREAMS) never leave the GPU, whatever the search radius -- a
+ *           batched rows kernel writes, per symbol, a 32-interval window of the quantised CDF chosen from the parameters
+ *           (33 exact boundaries; saturated ones from the closed form), a pop kernel walks each stream's state with one
+ *           warp and replays the reference's search literally for whatever falls outside the window (gmm_pop.cu);
+ *           smaller batches run the full-row kernel per stream and pop on a host thread (lowest latency for one stream);
  *   encode: one startfreq pass, then the serial push of the longest streams on the worker
  *           threads and of the rest on the GPU (push kernel, one warp per stream, gmm_push.cu),
  *           both at once, split by a cost model (FLASHGMM_PUSH=host|device|auto).
