@@ -331,7 +331,8 @@ struct flashgmm_ctx {
     PinBuf il_host;
     // device-resident decode (rows kernel -> pop kernel, nothing but symbols leaves the GPU)
     std::unique_ptr<DevDecode> dd;
-    int pop_min_streams = 4;          // batches at least this large decode on the device
+    int pop_min_streams = 4;          // batches at least this large may decode on the device
+    int pop_policy = 0;               // 0 cost model (want_device_pop), 1 always device, 2 always host
     int64_t pop_rows_budget = 256ll << 20;
     // device-resident encode (startfreq kernel -> push kernel): chosen per call by a cost model
     std::unique_ptr<DevEncode> de;

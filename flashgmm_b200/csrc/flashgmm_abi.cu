@@ -681,11 +681,31 @@ int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_strea
     return worst;
 }
 
+// Device pop (one warp per stream, ~53 ns per symbol whatever the number of streams) or host pop (full rows come down
+// over PCIe, a worker thread pops a stream at a few ns per symbol)? The device path's time is its longest stream; the
+// host path's is what the rows cost on the link (measured ~30 GB/s with several streams in flight) or the workers'
+// rounds. Small batches -- a few images of one pass, a single image's streams -- are faster on the host (measured for
+// 8 / 12 ELIC images per pass: 15.0 / 19.1 ms against 25.1 / 25.5 ms per batch); from ~16 images on, and whenever the
+// host has few cores, the device wins. FLASHGMM_POP_POLICY=device|host overrides, FLASHGMM_POP_MIN_STREAMS stays a floor.
 bool want_device_pop(const flashgmm_ctx* ctx, const flashgmm_stream* streams, int n_streams) {
     if (n_streams < ctx->pop_min_streams) return false;
     for (int i = 0; i < n_streams; ++i)
         if (streams[i].max_bs_value > kMaxDevicePopR) return false;
-    return true;
+    if (ctx->pop_policy == 1) return true;
+    if (ctx->pop_policy == 2) return false;
+    double row_bytes = 0, total_n = 0, max_n = 0;
+    for (int i = 0; i < n_streams; ++i) {
+        const double n = (double)streams[i].n;
+        if (streams[i].max_bs_value > kMaxTableR) return true;          // the host table is limited in radius
+        row_bytes += n * 2.0 * table_row_stride(streams[i].max_bs_value);
+        total_n += n;
+        max_n = std::max(max_n, n);
+    }
+    const double workers = (double)std::max(1, ctx->n_workers);
+    const double rounds = std::ceil((double)n_streams / workers);
+    const double host_s = std::max(row_bytes / 30e9, rounds * max_n * 6e-9) + 150e-6;
+    const double dev_s = max_n * 53e-9 + 200e-6;
+    return !(host_s < 0.8 * dev_s);
 }
 
 
@@ -1234,6 +1254,10 @@ int flashgmm_ctx_create(int device, flashgmm_ctx** out) {
     c->n_workers = (int)std::max<long>(1, env_long("FLASHGMM_WORKERS", std::min<long>(16, hw > 1 ? hw - 1 : 1)));
     c->pop_min_streams = (int)std::max<long>(1, env_long("FLASHGMM_POP_MIN_STREAMS", 4));
     c->pop_rows_budget = std::max<long>(1 << 20, env_long("FLASHGMM_POP_ROWS_BYTES", 256l << 20));
+    {
+        const char* pp = getenv("FLASHGMM_POP_POLICY");      // device | host | (unset) cost model
+        c->pop_policy = (pp && pp[0] == 'd') ? 1 : (pp && pp[0] == 'h') ? 2 : 0;
+    }
     {
         const char* pp = getenv("FLASHGMM_PUSH");            // host | device | (unset) auto
         c->push_policy = (pp && pp[0] == 'h') ? 1 : (pp && pp[0] == 'd') ? 2 : 0;

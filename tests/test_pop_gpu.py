@@ -23,6 +23,7 @@ def pop_ctx(monkeypatch):
 
     def make(rows_bytes=None):
         monkeypatch.setenv("FLASHGMM_POP_MIN_STREAMS", "1")
+        monkeypatch.setenv("FLASHGMM_POP_POLICY", "device")
         if rows_bytes is not None:
             monkeypatch.setenv("FLASHGMM_POP_ROWS_BYTES", str(rows_bytes))
         h = C.c_void_p()
@@ -185,24 +186,31 @@ def test_truncated_stream_reported_per_stream(pop_ctx):
     assert ov and np.array_equal(got[1], want1)          # zeros are fed past the end, like the oracle does
 
 
-def test_default_ctx_routes_batches_to_the_device_path():
-    """>= 4 streams through the public batch API: the pop kernel's launch shows up in the profile."""
+def test_default_ctx_routes_batches_by_the_cost_model():
+    """The public batch API on the default ctx: a batch of many long streams decodes on the device (the pop kernel's
+    launches show up in the profile), a handful of short streams on the host workers (no pop kernel launch) -- same
+    symbols either way."""
     from flashgmm_b200 import batch
     L = _lib.lib()
-    data = [synth.gmm_numpy(5000 + i, seed=800 + i) for i in range(6)]
-    streams = []
-    for sym, sg, mu, w in data:
-        b = port.gmm_encode(sym, sg, mu, w, 0)
-        streams.append((b, kmajor(sg, "cuda"), kmajor(mu, "cuda"), kmajor(w, "cuda"), synth.search_radius(sym)))
-    L.flashgmm_profile_reset()
-    L.flashgmm_profile_enable(1)
-    outs = batch.decode_batch(streams, 0)
-    L.flashgmm_profile_enable(0)
-    ms, nl, by = C.c_double(), C.c_uint64(), C.c_double()
-    _lib.check(L.flashgmm_profile_read(4, C.byref(ms), C.byref(nl), C.byref(by)))
-    assert nl.value >= 1 and ms.value > 0
-    for o, (sym, *_r) in zip(outs, data):
-        assert np.array_equal(o.cpu().numpy(), sym)
+
+    def run(sizes, seed):
+        data = [synth.gmm_numpy(n, seed=seed + i) for i, n in enumerate(sizes)]
+        streams = []
+        for sym, sg, mu, w in data:
+            b = port.gmm_encode(sym, sg, mu, w, 0)
+            streams.append((b, kmajor(sg, "cuda"), kmajor(mu, "cuda"), kmajor(w, "cuda"), synth.search_radius(sym)))
+        L.flashgmm_profile_reset()
+        L.flashgmm_profile_enable(1)
+        outs = batch.decode_batch(streams, 0)
+        L.flashgmm_profile_enable(0)
+        ms, nl, by = C.c_double(), C.c_uint64(), C.c_double()
+        _lib.check(L.flashgmm_profile_read(4, C.byref(ms), C.byref(nl), C.byref(by)))
+        for o, (sym, *_r) in zip(outs, data):
+            assert np.array_equal(o.cpu().numpy(), sym)
+        return nl.value
+
+    assert run([60000] * 32, 800) >= 1          # rows would cost more on the link than the warps' walk: device
+    assert run([5000 + i for i in range(6)], 850) == 0   # six short streams: host workers
 
 
 @pytest.mark.parametrize("n_streams", [1, 6])

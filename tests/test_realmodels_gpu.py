@@ -287,3 +287,20 @@ def test_state_dicts_load_strict_and_roundtrip(name, updated):
     enc2 = ref_net.latent_codec.compress(y)
     assert [s[0] for s in enc["strings"][:-1]] == [s[0] for s in enc2["strings"][:-1]]
     assert enc["strings"][-1] == enc2["strings"][-1]
+
+
+def test_model_flow_on_the_device_pop_path_too():
+    """Small batches decode on the host workers by the cost model (csrc/flashgmm_abi.cu::want_device_pop); the same model
+    tests must hold with every batch forced onto the rows + pop kernels (FLASHGMM_POP_POLICY is read at ctx creation:
+    child process)."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    if os.environ.get("FLASHGMM_POP_POLICY"):
+        pytest.skip("already forced")
+    env = dict(os.environ, FLASHGMM_POP_POLICY="device")
+    r = subprocess.run([sys.executable, "-m", "pytest", str(Path(__file__)), "-q", "-x", "-m", "gpu", "-k",
+                        "batch_streams_equal or plausible_parameters"], env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0 and " passed" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
