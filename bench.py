@@ -652,10 +652,21 @@ def sweep_modes_and_radius(torch, synth, L, _lib, dev, n=1 << 22, iters=5):
     del out
     streams = [synth.gmm_torch(147456, seed=900 + i, device=dev) for i in range(24)]
     R0 = max(int(s[0].abs().max().item()) for s in streams) + 2
+    # a ctx that always takes the device path (the cost model sends passes with small rows to the host workers): these
+    # entries are about the rows / pop KERNELS
+    old_policy = os.environ.get("FLASHGMM_POP_POLICY")
+    os.environ["FLASHGMM_POP_POLICY"] = "device"
+    try:
+        dctx = _lib.new_ctx(dev.index)
+    finally:
+        if old_policy is None:
+            del os.environ["FLASHGMM_POP_POLICY"]
+        else:
+            os.environ["FLASHGMM_POP_POLICY"] = old_policy
 
     def decode_pass(mode, R):
         bs = [x.copy() for x in EncodeJob(streams, mode).run()]
-        job = DecodeJob([(a, b, c, R) for (_, a, b, c) in streams], mode)
+        job = DecodeJob([(a, b, c, R) for (_, a, b, c) in streams], mode, ctx=dctx)
         outs = job.run(bs)
         assert all(torch.equal(o, s[0]) for o, s in zip(outs, streams))
         L.flashgmm_profile_reset()

@@ -71,6 +71,10 @@ __device__ __forceinline__ float exp256(float x) {
 template <int MODE>
 __device__ __forceinline__ float phi(float t);
 
+// (Round 2 also tried a branch-free square root for 1 - exp(.) in [0, 1] -- MUFU.RSQ seed, one coupled Newton step, one
+// residual correction -- to drop __fsqrt_rn's range check and slow-path call, 10 % of the rows kernel's instructions
+// being BSSY / BRA / BSYNC. The exhaustive device comparison against __fsqrt_rn found mismatches, and it was 4 % SLOWER
+// in both the startfreq and the rows kernel. Rejected.)
 template <>
 __device__ __forceinline__ float phi<MODE_POLYA>(float t) {
     float a = __fmul_rn(FGMM_M2_OVER_PI, __fmul_rn(t, t));
