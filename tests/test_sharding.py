@@ -92,3 +92,17 @@ def test_two_ranks_code_their_shares_and_agree_on_the_job(tmp_path):
 def test_single_process_needs_no_process_group():
     assert shard.max_over_ranks(0.5) == 0.5
     assert shard.gather_item_sizes(3, [(0, 10), (2, 30)]) == [10, -1, 30]
+
+
+def test_sharded49_job_is_dealt_evenly():
+    """BASELINE.json configs[4] as bench.py --workload sharded49 builds it: 24 images + a 3840x2160 image as 5 x 5 tiles of
+    768x512 = 49 equal-cost items; every rank count of one box gets them all exactly once, loads differ by at most one."""
+    tiles = shard.tile_image(2160, 3840)
+    assert len(tiles) == 25 and tiles[-1].pad_h == 2560 - 2160 and all(t.pad_w == 0 for t in tiles)
+    costs = [1.0] * (24 + len(tiles))
+    for world in (1, 2, 4, 8):
+        parts = shard.assign(costs, world)
+        assert sorted(i for p in parts for i in p) == list(range(49))
+        sizes = [len(p) for p in parts]
+        assert max(sizes) - min(sizes) <= 1
+        assert [shard.my_items(costs, world, r) for r in range(world)] == parts
