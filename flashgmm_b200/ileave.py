@@ -40,9 +40,11 @@ def _landing_zone(cap: int):
     return _zone.numpy()[:cap]
 
 
-def encode(symbols, scales, means, weights, R: int, mode=None, segment_log2: int = 0) -> bytes:
+def encode(symbols, scales, means, weights, R: int, mode=None, segment_log2: int = 0, as_view: bool = False):
     """Symbols outside ``[-R, R]`` (and symbols the model gives zero mass) are escaped as raw
-    int32, so ``R`` trades search depth in the decoder against escapes: any ``R >= 0`` round-trips."""
+    int32, so ``R`` trades search depth in the decoder against escapes: any ``R >= 0`` round-trips.
+    -> ``bytes``; with ``as_view=True`` a uint8 numpy view of the page-locked landing zone instead (valid until the next
+    ``encode`` call of this process): a fresh 7 MB ``bytes`` object costs more host time than the whole device side."""
     sym = _tensor(symbols, torch.int32)
     if sym.dim() != 1:
         raise ValueError("symbols must be 1-D")
@@ -68,7 +70,7 @@ def encode(symbols, scales, means, weights, R: int, mode=None, segment_log2: int
                 cap = n_out.value
                 continue
             _lib.check(rc)
-            return out[: n_out.value].tobytes()
+            return out[: n_out.value] if as_view else out[: n_out.value].tobytes()
     raise RuntimeError("unreachable")
 
 
