@@ -8,6 +8,7 @@ identical to ``RansEncoder.encode_with_indexes_gmm`` on that stream alone.
 from __future__ import annotations
 
 import ctypes as C
+import threading
 from typing import List, Sequence, Tuple
 
 import numpy as np
@@ -17,16 +18,32 @@ from . import _lib
 from .ans import _dev_index, _gmm_views, _tensor, get_approx_mode
 
 
+_tls = threading.local()
+
+
+def _arena(nbytes: int) -> np.ndarray:
+    """Per-thread landing zone for the bitstreams of a one-shot ``encode_batch`` (its results leave as ``bytes``
+    copies, so the next call may write over it): fresh ``np.empty`` buffers would be page-faulted in by the push
+    workers on every call."""
+    a = getattr(_tls, "arena", None)
+    if a is None or a.size < nbytes:
+        a = _tls.arena = np.empty(max(nbytes, 1 << 20) * 5 // 4, np.uint8)
+    return a
+
+
 class EncodeJob:
     """Pre-bound encode call over fixed tensors (re-usable: no per-call allocation)."""
 
-    def __init__(self, streams: Sequence[Tuple], mode=None, ctx=None):
+    def __init__(self, streams: Sequence[Tuple], mode=None, ctx=None, shared_arena: bool = False):
         self.mode = get_approx_mode() if mode is None else mode
         self.n_streams = len(streams)
         self.arr = (_lib.Stream * max(1, self.n_streams))()
         self._keep = []
         self.outs: List[np.ndarray] = []
         self.device = None
+        arena, used = None, 0
+        if shared_arena:
+            arena = _arena(sum(max(64, (int(st[0].numel()) * 9) // 4 + 64) + 64 for st in streams))
         for i, (sym, sc, mu, w) in enumerate(streams):
             sym = _tensor(sym, torch.int32).contiguous()
             (sc, mu, w), N, (sn, sk), dev = _gmm_views(sc, mu, w, sym.numel())
@@ -36,7 +53,12 @@ class EncodeJob:
                 self.device = dev
             elif dev != self.device:
                 raise ValueError("all streams of a batch must be on one device")
-            out = np.empty(max(64, (N * 9) // 4 + 64), np.uint8)
+            cap = max(64, (N * 9) // 4 + 64)
+            if arena is None:
+                out = np.empty(cap, np.uint8)
+            else:
+                out = arena[used: used + cap]
+                used += (cap + 63) & ~63
             self._keep += [sym, sc, mu, w]
             self.outs.append(out)
             a = self.arr[i]
@@ -106,7 +128,7 @@ def _sync_inputs(dev):
 
 def encode_batch(streams: Sequence[Tuple], mode=None) -> List[bytes]:
     """streams: (symbols, scales, means, weights) per stream -> list of bytes."""
-    job = EncodeJob(streams, mode)
+    job = EncodeJob(streams, mode, shared_arena=True)
     _sync_inputs(job.device)
     return [v.tobytes() for v in job.run()]
 

@@ -330,7 +330,7 @@ Lane& lane_of(flashgmm_ctx* ctx, int idx) {
 constexpr int32_t kMaxDevicePopR = kPopWindowMaxR;   // wider searches stay on the host path
 
 int decode_batch_device(flashgmm_ctx* ctx, flashgmm_stream* streams, int n_streams, int mode, int mem) {
-    std::lock_guard<std::mutex> g(ctx->mu);
+    std::lock_guard<std::mutex> lock(ctx->mu);
     CU_TRY(cudaSetDevice(ctx->device));
     if (!ctx->dd) ctx->dd.reset(new DevDecode());
     DevDecode& D = *ctx->dd;

@@ -19,27 +19,51 @@ from __future__ import annotations
 
 import os
 import warnings
-from typing import Callable, Dict, Sequence, Tuple
+from typing import Callable, Dict, List, Sequence, Tuple
 
 import torch
 from torch import Tensor
 
 
+_side_streams: Dict[torch.device, List["torch.cuda.Stream"]] = {}
+
+
+def _branch_streams(dev: torch.device, n: int) -> List["torch.cuda.Stream"]:
+    """Side streams the images of a group are captured on (shared by all captures of a device: they only carry work
+    while a capture or its warm-up is in progress)."""
+    pool = _side_streams.setdefault(dev, [])
+    while len(pool) < n:
+        pool.append(torch.cuda.Stream(device=dev))
+    return pool[:n]
+
+
 class _Captured:
     """One captured instance of a step: static inputs / outputs for `group` images, its graph, and the side stream it
     replays on. With group > 1 the graph contains the step `group` times, each on ONE image (batch-1 shapes, so every
-    image gets exactly the kernels and summation orders of coding it alone) -- one replay then serves several images."""
+    image gets exactly the kernels and summation orders of coding it alone), as `group` PARALLEL branches: the images
+    are captured on side streams forked from and joined to the capture stream, so a replay runs `group` independent
+    chains of small kernels side by side instead of one chain `group` times as long."""
 
     def __init__(self, fn: Callable[..., Tuple[Tensor, ...]], example: Sequence[Tensor], group: int = 0):
         dev = example[0].device
         self.group = group
         self.inputs = [t.detach().clone() for t in example]
         self.stream = torch.cuda.Stream(device=dev)
+        branches = _branch_streams(dev, group) if group > 1 else []
 
         def run():
             if group <= 0:
                 return fn(*self.inputs)
-            per = [fn(*(t[g:g + 1] for t in self.inputs)) for g in range(group)]
+            if group == 1:
+                return fn(*(t[0:1] for t in self.inputs))
+            main = torch.cuda.current_stream(dev)
+            per = []
+            for g, side in enumerate(branches):               # fork: one branch per image
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    per.append(fn(*(t[g:g + 1] for t in self.inputs)))
+            for side in branches:                             # join
+                main.wait_stream(side)
             return tuple(torch.cat([o[j] for o in per], dim=0) for j in range(len(per[0])))
 
         self.stream.wait_stream(torch.cuda.current_stream(dev))
@@ -47,6 +71,7 @@ class _Captured:
             for _ in range(2):                                # library warm-up outside the capture
                 run()
         torch.cuda.current_stream(dev).wait_stream(self.stream)
+        torch.cuda.synchronize(dev)                           # the branch streams are idle before the capture starts
         self.graph = torch.cuda.CUDAGraph()
         with torch.no_grad(), torch.cuda.graph(self.graph):
             self.outputs = run()
