@@ -75,6 +75,7 @@ _SIGS = {
                                                _vp, _vp]),
     "flashgmm_gmm_epilogue_scatter": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _vp, _vp]),
     "flashgmm_gmm_prologue_scan_batch": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
+    "flashgmm_gmm_prologue_scan_batch_noalloc": (C.c_int, [C.c_int, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
     "flashgmm_gmm_prologue_gather_batch": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, C.c_int, _vp, _vp, _vp,
                                                      _vp, _vp, _vp]),
     "flashgmm_gmm_epilogue_scatter_batch": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp]),

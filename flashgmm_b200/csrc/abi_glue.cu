@@ -81,6 +81,40 @@ int flashgmm_gmm_prologue_scan_batch(flashgmm_ctx* ctx, const float* y_d, int64_
     return scan_impl(ctx, y_d, B, C, HW, yq_out_d, bitmap_out_d, bitmap_out_h, extrema_out_h, stream);
 }
 
+// No counterpart in the reference: the batch scan for callers that
+// cannot allocate. The scratch is the file-scope device array of gmm_prologue.cu; the host results go straight into
+// the caller's buffers. No cudaMalloc / cudaFree / cudaHostAlloc, no ctx (a ctx owns growable buffers).
+static_assert(kStaticScanMaxWords == FLASHGMM_NOALLOC_SCAN_MAX_WORDS, "the header states the array's size");
+int flashgmm_gmm_prologue_scan_batch_noalloc(int device, const float* y_d, int64_t B, int64_t C, int64_t HW,
+                                             float* yq_out_d, int64_t* bitmap_out_d, int32_t* bitmap_out_h,
+                                             float* extrema_out_h, void* stream) {
+    if (B < 0 || C < 0 || HW < 0 || C > (1 << 20) || B > (1 << 16))
+        return fail(FLASHGMM_EINVAL, "bad shape B=%lld C=%lld HW=%lld", (long long)B, (long long)C, (long long)HW);
+    if (B * C + 2 * B > kStaticScanMaxWords)
+        return fail(FLASHGMM_EINVAL, "B*(C+2) = %lld words of scratch exceed the static maximum of %lld (use "
+                    "flashgmm_gmm_prologue_scan_batch, which allocates)", (long long)(B * C + 2 * B),
+                    (long long)kStaticScanMaxWords);
+    if (B > 0 && C > 0 && HW > 0 && (!y_d || !yq_out_d)) return fail(FLASHGMM_EINVAL, "null tensor");
+    if (B > 0 && (!bitmap_out_h || !extrema_out_h)) return fail(FLASHGMM_EINVAL, "null host output");
+    if (B == 0) return FLASHGMM_OK;
+    CU_TRY(cudaSetDevice(device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const uint32_t* scratch = nullptr;
+    CU_TRY(launch_gmm_prologue_scan_static(y_d, (int)B, (int)C, HW, yq_out_d, reinterpret_cast<long long*>(bitmap_out_d),
+                                           &scratch, st));
+    g_launches.fetch_add(C > 0 ? 2 : 1, std::memory_order_relaxed);
+    CU_TRY(cudaMemcpyAsync(extrema_out_h, scratch, (size_t)(2 * B) * 4, cudaMemcpyDeviceToHost, st));
+    if (C > 0) CU_TRY(cudaMemcpyAsync(bitmap_out_h, scratch + 2 * B, (size_t)(B * C) * 4, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    const bool empty = C == 0 || HW == 0;
+    for (int64_t i = 0; i < 2 * B; ++i) {                    // order-preserving codes -> floats, in place
+        uint32_t code;
+        memcpy(&code, extrema_out_h + i, 4);
+        extrema_out_h[i] = empty ? 0.0f : gmm_extremum_from_bits(code);
+    }
+    return FLASHGMM_OK;
+}
+
 int flashgmm_gmm_prologue_gather_batch(flashgmm_ctx* ctx, const float* yq_d, const float* scales_d, const float* means_d,
                                        const float* weights_d, const int64_t* bitmap_d, int64_t B, int64_t C, int64_t HW,
                                        int K, const int64_t* n_sym_h, int32_t* symbols_out_d, float* scales_out_d,

@@ -136,6 +136,13 @@ struct PrologueBatch { int64_t off[kPrologueMaxBatch]; int64_t n[kPrologueMaxBat
 // extrema: 2 words per image (order-preserving codes of max and min of the unrounded y)
 cudaError_t launch_gmm_prologue_scan(const float* y, int B, int C, int64_t HW, float* yq, long long* bitmap64,
                                      int32_t* bitmap32, uint32_t* extrema, cudaStream_t st);
+// The same scan with its scratch (extrema codes, bitmap words: 2B + B*C uint32) in a file-scope __device__ array of
+// kStaticScanMaxWords words instead of a caller / ctx buffer: allocates nothing. *scratch_out = the array's DEVICE
+// address on the current device ([0, 2B) extrema codes, then the B*C bitmap words). cudaErrorInvalidValue beyond the
+// maximum. Calls share the array: calls that overlap on the GPU race.
+constexpr int64_t kStaticScanMaxWords = 65536;          // 256 KiB per GPU, held until exit
+cudaError_t launch_gmm_prologue_scan_static(const float* y, int B, int C, int64_t HW, float* yq, long long* bitmap64,
+                                            const uint32_t** scratch_out, cudaStream_t st);
 cudaError_t launch_gmm_prologue_gather(const float* yq, const float* scales, const float* means, const float* weights,
                                        const long long* bitmap, int B, int C, int64_t HW, int K, const PrologueBatch& meta,
                                        int32_t* sym_out, float* scales_out, float* means_out, float* weights_out,

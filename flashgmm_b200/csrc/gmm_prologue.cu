@@ -17,6 +17,8 @@
 // views with strides (1, Nsym) the coder reads.
 #include "gmm_kernels.h"
 
+#include <mutex>
+
 namespace flashgmm {
 
 namespace {
@@ -166,6 +168,59 @@ cudaError_t launch_gmm_epilogue_scatter(const int32_t* symbols, const long long*
                                         const PrologueBatch& meta, float* y_hat, cudaStream_t st) {
     if (B <= 0 || C <= 0 || HW <= 0) return cudaSuccess;
     gmm_epilogue_scatter_kernel<<<dim3((unsigned)C, (unsigned)B), kPrThreads, 0, st>>>(symbols, bitmap, C, HW, meta, y_hat);
+    return cudaGetLastError();
+}
+
+// ---- the scan with its scratch in a file-scope array: nothing is allocated, ever ------------------
+// (no counterpart in the reference; for callers that cannot call cudaMalloc). Layout of the scratch,
+// as in the allocating path: [0, 2B) extrema codes, then B*C bitmap words. Every GPU that loads the
+// library holds these kStaticScanMaxWords * 4 bytes until exit; every call shares them, the array keeps
+// the previous call's contents (the extrema codes are reset by the kernel below on every call, the
+// bitmap words of the call's B*C channels are all overwritten), and two calls that overlap on the GPU
+// race on it.
+static __device__ __align__(256) uint32_t g_static_scan_scratch[kStaticScanMaxWords];
+
+namespace {
+
+// extrema[2b] collects the max (starts at the smallest code), extrema[2b+1] the min (the largest)
+__global__ void gmm_static_scan_reset_kernel(int B) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < B) { g_static_scan_scratch[2 * b] = 0u; g_static_scan_scratch[2 * b + 1] = 0xffffffffu; }
+}
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+uint32_t* g_static_scan_addr[kMaxDevices] = {};       // DEVICE address of the array, per device
+
+}  // namespace
+
+cudaError_t launch_gmm_prologue_scan_static(const float* y, int B, int C, int64_t HW, float* yq, long long* bitmap64,
+                                            const uint32_t** scratch_out, cudaStream_t st) {
+    // In host code `g_static_scan_scratch` is a host-side stand-in, not a device address: the address
+    // the kernel gets comes from cudaGetSymbolAddress, resolved once per device with that device current.
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    uint32_t* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_static_mu);
+        if (!g_static_scan_addr[dev]) {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_static_scan_scratch);
+            if (e != cudaSuccess) return e;
+            g_static_scan_addr[dev] = static_cast<uint32_t*>(p);
+        }
+        scratch = g_static_scan_addr[dev];
+    }
+    if (scratch_out) *scratch_out = scratch;
+    if (B <= 0) return cudaSuccess;
+    if ((int64_t)B * C + 2 * (int64_t)B > kStaticScanMaxWords) return cudaErrorInvalidValue;
+    gmm_static_scan_reset_kernel<<<(unsigned)((B + 255) / 256), 256, 0, st>>>(B);
+    e = cudaGetLastError();
+    if (e != cudaSuccess || C <= 0) return e;
+    gmm_prologue_scan_kernel<<<(unsigned)(B * C), kPrThreads, 0, st>>>(y, C, HW, yq, bitmap64,
+                                                                      reinterpret_cast<int32_t*>(scratch + 2 * B), scratch);
     return cudaGetLastError();
 }
 

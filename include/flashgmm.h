@@ -221,6 +221,22 @@ int flashgmm_gmm_epilogue_scatter(flashgmm_ctx* ctx, const int32_t* symbols_d, c
 int flashgmm_gmm_prologue_scan_batch(flashgmm_ctx* ctx, const float* y_d, int64_t B, int64_t C, int64_t HW,
                                      float* y_quantized_out_d, int64_t* bitmap_out_d, int32_t* bitmap_out_h,
                                      float* extrema_out_h, void* stream);
+/* flashgmm_gmm_prologue_scan_batch for callers that cannot allocate (code under CUDA-graph capture set-up, tight
+ * serving loops, harnesses that forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, outputs and results as flashgmm_gmm_prologue_scan_batch, but no ctx (a ctx owns
+ * growable buffers): the kernel's scratch (2 extrema codes per image + one bitmap word per channel) lives in a
+ * file-scope __device__ array of FLASHGMM_NOALLOC_SCAN_MAX_WORDS 32-bit words (256 KiB; every GPU that loads the
+ * library holds it until exit), and the host results are copied straight into bitmap_out_h / extrema_out_h. The call
+ * makes no cudaMalloc / cudaFree / cudaHostAlloc and calls no allocating library routine. B * (C + 2) must not
+ * exceed FLASHGMM_NOALLOC_SCAN_MAX_WORDS: FLASHGMM_EINVAL otherwise (24 ELIC images are 24 * 322 = 7728).
+ * `device`: CUDA device ordinal of y_d; made current. Two launches, two small copies, one synchronisation of
+ * `stream`. All calls on a device share the array (it keeps the previous call's contents; what must start clean
+ * is reset on every call): calls that OVERLAP on the GPU -- two host threads, two streams -- race; serialise them.
+ * The first call on a device resolves the array's device address (cudaGetSymbolAddress). */
+#define FLASHGMM_NOALLOC_SCAN_MAX_WORDS 65536
+int flashgmm_gmm_prologue_scan_batch_noalloc(int device, const float* y_d, int64_t B, int64_t C, int64_t HW,
+                                             float* y_quantized_out_d, int64_t* bitmap_out_d, int32_t* bitmap_out_h,
+                                             float* extrema_out_h, void* stream);
 int flashgmm_gmm_prologue_gather_batch(flashgmm_ctx* ctx, const float* y_quantized_d, const float* scales_d,
                                        const float* means_d, const float* weights_d, const int64_t* bitmap_d,
                                        int64_t B, int64_t C, int64_t HW, int K, const int64_t* n_sym_h,
