@@ -37,6 +37,7 @@ import os
 import statistics
 import subprocess
 import sys
+import threading
 import time
 from pathlib import Path
 
@@ -517,13 +518,24 @@ def run_b200(args):
     if micro:
         line["microbench"] = micro
     if world == 1 and not args.no_microbench:
-        line["mode_and_radius_sweep"] = sweep_modes_and_radius(torch, synth, L, _lib, dev)
-        line["likelihood"] = likelihood_bench(torch, L, _lib, dev)
-        line["model_codec"] = model_codec_bench(torch, dev, B)
-        line["model_codec_single_image"] = model_codec_bench(torch, dev, 1, reps=5)      # what the reference's eval scripts do
+        # side measurements: a failure in one of them is recorded in its place, the headline line is still printed
+        def extra(key, fn):
+            try:
+                line[key] = fn()
+            except (Exception, SystemExit) as e:              # noqa: BLE001
+                line[key] = {"error": f"{type(e).__name__}: {e}"[:300]}
+
+        extra("mode_and_radius_sweep", lambda: sweep_modes_and_radius(torch, synth, L, _lib, dev))
+        extra("likelihood", lambda: likelihood_bench(torch, L, _lib, dev))
+        extra("model_codec", lambda: model_codec_bench(torch, dev, B))
+        extra("model_codec_single_image", lambda: model_codec_bench(torch, dev, 1, reps=5))   # what the reference's eval scripts do
+        extra("model_codec_two_lanes", lambda: model_codec_bench(torch, dev, B, reps=3, lanes=2))
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_sample(batches[0][0], radii[0][0])
-        full = reference_full_call(torch, dev)
+        try:
+            full = reference_full_call(torch, dev)
+        except Exception as e:                                # noqa: BLE001
+            full = {"error": f"{type(e).__name__}: {e}"[:300]}
         if full:
             line["cpu_baseline_full_call"] = full
     emit(line)
@@ -749,7 +761,7 @@ def likelihood_bench(torch, L, _lib, dev, iters=20):
     return res
 
 
-def model_codec_bench(torch, dev, B=24, reps=3):
+def model_codec_bench(torch, dev, B=24, reps=3, lanes=1):
     """The MODEL-facing path: `latent_codec.compress / decompress` of the ELIC2022GMM architecture for a
     batch of B images through flashgmm_b200's pass codecs -- hyper branch (h_a, z table coder, h_s), 5 channel groups x 2
     checkerboard passes, every network step replayed from a CUDA graph per image, scan / gather / scatter kernels per pass,
@@ -787,11 +799,14 @@ def model_codec_bench(torch, dev, B=24, reps=3):
     for i, codec in enumerate(codecs):
         def fake(ctx_params, codec=codec, i=i, real=codec._mixture):
             real(ctx_params)                                  # the entropy-parameter head and the softmax still run
-            n = calls.get(i, 0)
-            calls[i] = n + 1
+            key = (threading.get_ident(), i)                  # passes alternate per codec and per calling thread
+            n = calls.get(key, 0)
+            calls[key] = n + 1
             return (*tables[(i, n % 2)], None)
         codec._mixture = fake
     lc = net.latent_codec
+    if lanes > 1:
+        return _model_codec_lanes(torch, dev, lc, y, lanes, reps)
     enc = lc.compress(y)
     dec = lc.decompress(enc["strings"], enc["shape"])
     if not torch.equal(dec["y_hat"], torch.round(y)):
@@ -819,6 +834,74 @@ def model_codec_bench(torch, dev, B=24, reps=3):
             "graph_captures": r.captures, "graph_replays": r.replays, "net_batching": r.mode,
             "note": "host wall clock of latent_codec.compress / decompress incl. h_a / h_s, z coder, context and parameter "
                     "networks (CUDA-graph replays per image), glue kernels, batched coder; one batch in flight"}
+
+
+def _model_codec_lanes(torch, dev, lc, y, n_lanes, reps):
+    """The same model path with `n_lanes` batches in flight: one host thread per flashgmm_b200.Lane (own library ctx, own
+    CUDA graphs, own stream), every thread compresses and decompresses its own batch of B images `reps` times; the model
+    is shared. Wall clock over all threads, after each lane has run once on its own (graph captures)."""
+    import flashgmm_b200 as fg
+    lanes = [fg.Lane(device=dev.index or 0) for _ in range(n_lanes)]
+    want = torch.round(y)
+    for lane in lanes:                                        # captures, buffers; also the correctness gate per lane
+        with lane:
+            enc = lc.compress(y)
+            dec = lc.decompress(enc["strings"], enc["shape"])
+            ok = torch.equal(dec["y_hat"], want)
+        if not ok:
+            raise SystemExit("model codec (lanes) round trip mismatch: refusing to report a number")
+    torch.cuda.synchronize()
+    errors, t_c, t_d = [], [0.0] * n_lanes, [0.0] * n_lanes
+    gate = threading.Barrier(n_lanes + 1)
+
+    def work(k):
+        try:
+            with lanes[k]:
+                gate.wait()
+                for _ in range(reps):
+                    t0 = time.perf_counter()
+                    enc = lc.compress(y)
+                    torch.cuda.current_stream().synchronize()
+                    t1 = time.perf_counter()
+                    dec = lc.decompress(enc["strings"], enc["shape"])
+                    torch.cuda.current_stream().synchronize()
+                    t_c[k] += (t1 - t0) / reps
+                    t_d[k] += (time.perf_counter() - t1) / reps
+                if not torch.equal(dec["y_hat"], want):
+                    errors.append(f"lane {k}: round trip mismatch")
+        except Exception as e:                                # noqa: BLE001
+            errors.append(f"lane {k}: {type(e).__name__}: {e}")
+            try:
+                gate.abort()
+            except Exception:
+                pass
+
+    # a thread that comes back from a library call (GIL released) has to get the GIL back from a thread that is busy
+    # issuing small torch ops and gives it up only every `switch interval` (5 ms by default): dozens of such hand-overs
+    # per coding call
+    old_interval = sys.getswitchinterval()
+    sys.setswitchinterval(float(os.environ.get("FLASHGMM_BENCH_SWITCH_INTERVAL", "2e-4")))
+    threads = [threading.Thread(target=work, args=(k,)) for k in range(n_lanes)]
+    for t in threads:
+        t.start()
+    gate.wait()
+    t0 = time.perf_counter()
+    for t in threads:
+        t.join()
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    interval = sys.getswitchinterval()
+    sys.setswitchinterval(old_interval)
+    if errors:
+        raise SystemExit("model codec (lanes): " + "; ".join(errors))
+    B, nsym = y.size(0), y.numel()
+    return {"lanes": n_lanes, "images_per_batch": B, "batches": n_lanes * reps,
+            "ms_per_batch": round(1e3 * wall / (n_lanes * reps), 2),
+            "ms_per_image": round(1e3 * wall / (n_lanes * reps * B), 3),
+            "value_msym_s": round(2 * nsym * n_lanes * reps / wall / 1e6, 1),
+            "compress_ms_in_lane": round(1e3 * sum(t_c) / n_lanes, 2), "decompress_ms_in_lane": round(1e3 * sum(t_d) / n_lanes, 2),
+            "python_switch_interval_s": interval,
+            "note": "compress + decompress of every batch through latent_codec.*, one host thread per Lane; wall clock over all lanes"}
 
 
 def reference_full_call(torch, dev, repeat=3):

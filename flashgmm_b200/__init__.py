@@ -13,3 +13,4 @@ from .ans import (RansDecoder, RansEncoder, get_approx_mode, gmm_decode, gmm_enc
 from .entropy_models import EntropyBottleneck, GaussianMixtureConditional, LowerBound  # noqa: F401,E402
 from .latent_codecs import (ChannelGroupsLatentCodec, CheckerboardLatentCodec,  # noqa: F401,E402
                             GaussianMixtureConditionalLatentCodec, HyperLatentCodec, HyperpriorLatentCodec, mount)
+from .lanes import Lane  # noqa: F401,E402

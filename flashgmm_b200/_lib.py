@@ -138,8 +138,17 @@ def check(code: int):
     raise FlashGMMError(code, msg)
 
 
+_tls = threading.local()
+
+
 def ctx(device: int = 0):
-    """Per-device context handle (created on first use, kept for the process)."""
+    """Per-device context handle (created on first use, kept for the process). A thread inside a
+    ``flashgmm_b200.Lane`` gets the lane's own ctx instead (``bind_thread_ctx``)."""
+    own = getattr(_tls, "ctxs", None)
+    if own:
+        h = own.get(device)
+        if h is not None:
+            return h
     h = _ctxs.get(device)
     if h is None:
         with _lock:
@@ -161,6 +170,20 @@ def new_ctx(device: int = 0):
 
 
 _extra_ctxs: list = []
+
+
+def bind_thread_ctx(device: int, handle) -> object:
+    """Make ``ctx(device)`` return ``handle`` on the CALLING thread (``None`` removes the binding).
+    -> the previous binding, to restore."""
+    own = getattr(_tls, "ctxs", None)
+    if own is None:
+        own = _tls.ctxs = {}
+    prev = own.get(device)
+    if handle is None:
+        own.pop(device, None)
+    else:
+        own[device] = handle
+    return prev
 
 
 def launch_count() -> int:

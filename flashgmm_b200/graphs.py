@@ -18,6 +18,7 @@ orders) for different batch sizes, and the decoder must reproduce the encoder's 
 from __future__ import annotations
 
 import os
+import threading
 import warnings
 from typing import Callable, Dict, List, Sequence, Tuple
 
@@ -25,13 +26,13 @@ import torch
 from torch import Tensor
 
 
-_side_streams: Dict[torch.device, List["torch.cuda.Stream"]] = {}
+_side_streams: Dict[tuple, List["torch.cuda.Stream"]] = {}
 
 
 def _branch_streams(dev: torch.device, n: int) -> List["torch.cuda.Stream"]:
-    """Side streams the images of a group are captured on (shared by all captures of a device: they only carry work
-    while a capture or its warm-up is in progress)."""
-    pool = _side_streams.setdefault(dev, [])
+    """Side streams the images of a group are captured on (shared by all captures of a device made by one host thread:
+    they only carry work while a capture or its warm-up is in progress, and a stream can be part of one capture only)."""
+    pool = _side_streams.setdefault((dev, threading.get_ident()), [])
     while len(pool) < n:
         pool.append(torch.cuda.Stream(device=dev))
     return pool[:n]
@@ -73,7 +74,8 @@ class _Captured:
         torch.cuda.current_stream(dev).wait_stream(self.stream)
         torch.cuda.synchronize(dev)                           # the branch streams are idle before the capture starts
         self.graph = torch.cuda.CUDAGraph()
-        with torch.no_grad(), torch.cuda.graph(self.graph):
+        # "thread_local": other host threads (further lanes, the library's workers) may allocate while this one captures
+        with torch.no_grad(), torch.cuda.graph(self.graph, stream=self.stream, capture_error_mode="thread_local"):
             self.outputs = run()
 
     def __call__(self, *tensors: Tensor) -> Tuple[Tensor, ...]:
@@ -169,10 +171,29 @@ class NetRunner:
 
 
 _default = None
+_tls = threading.local()
 
 
 def default_runner() -> NetRunner:
+    """The runner of modules that were not given one by ``mount(net, runner=...)``: the calling thread's
+    (``bind_thread_runner``, used by ``flashgmm_b200.Lane``) or the process-wide one. A runner's captured graphs have
+    static input / output buffers, so two host threads must never replay through the same runner."""
+    own = getattr(_tls, "runner", None)
+    if own is not None:
+        return own
     global _default
     if _default is None:
         _default = NetRunner()
     return _default
+
+
+def thread_runner():
+    """The runner bound to the calling thread, or None."""
+    return getattr(_tls, "runner", None)
+
+
+def bind_thread_runner(runner):
+    """Make ``default_runner()`` return ``runner`` on the CALLING thread (``None`` removes the binding). -> the previous one."""
+    prev = getattr(_tls, "runner", None)
+    _tls.runner = runner
+    return prev

@@ -46,7 +46,7 @@ import torch.nn.functional as F
 from torch import Tensor
 
 from .entropy_models import EncodeSession, EntropyBottleneck, GaussianMixtureConditional, PendingStream
-from .graphs import NetRunner, default_runner
+from .graphs import NetRunner, default_runner, thread_runner
 
 
 def quantize_ste(x: Tensor) -> Tensor:
@@ -89,7 +89,9 @@ def _finish(strings):
 
 
 def _runner_of(module) -> NetRunner:
-    return getattr(module, "_net_runner", None) or default_runner()
+    """The calling thread's runner inside a ``Lane`` (graphs have static buffers: one runner per host thread), else the
+    one ``mount(net, runner=...)`` gave the module, else the process-wide default."""
+    return thread_runner() or getattr(module, "_net_runner", None) or default_runner()
 
 
 def _wkey(module: nn.Module, tag: str):

@@ -250,3 +250,32 @@ def test_mount_is_idempotent_and_keeps_own_classes():
     before = {id(m) for m in net.modules()}
     assert fg.mount(net) is net and fg.mount(net) is net
     assert {id(m) for m in net.modules()} == before          # nothing to swap in a tree built from this package's classes
+
+
+def test_thread_bindings_of_ctx_and_runner_are_per_thread():
+    """flashgmm_b200.Lane's plumbing: a ctx / runner bound on one thread is invisible on another."""
+    import threading
+    from flashgmm_b200 import _lib
+    from flashgmm_b200.graphs import NetRunner, bind_thread_runner, default_runner, thread_runner
+    a, b = object(), object()
+    seen = {}
+    assert _lib.bind_thread_ctx(3, a) is None
+    r_main = NetRunner(graphs=False)
+    assert bind_thread_runner(r_main) is None
+
+    def other():
+        seen["ctx_before"] = getattr(_lib._tls, "ctxs", None)
+        _lib.bind_thread_ctx(3, b)
+        seen["ctx"] = _lib.ctx(3)
+        seen["runner"] = thread_runner()
+
+    t = threading.Thread(target=other)
+    t.start()
+    t.join()
+    try:
+        assert not seen["ctx_before"] and seen["ctx"] is b and seen["runner"] is None
+        assert _lib.ctx(3) is a and default_runner() is r_main
+    finally:
+        assert _lib.bind_thread_ctx(3, None) is a
+        assert bind_thread_runner(None) is r_main
+    assert thread_runner() is None

@@ -226,6 +226,47 @@ def test_graph_replay_equals_eager():
         assert [x[0] for x in a] == [x[0] for x in b]
 
 
+def test_lanes_two_threads_on_one_model_give_the_single_thread_bytes():
+    """flashgmm_b200.Lane: two host threads code different batches through the SAME model concurrently (own ctx, own
+    graphs, own stream each); every stream equals what the plain single-thread call produces."""
+    import threading
+    net = build("elic")
+    ys = [latent(net, B=2, seed=21 + k, hw=(256, 384)) for k in range(2)]
+    want = [net.latent_codec.compress(y) for y in ys]
+    torch.cuda.synchronize()
+    lanes = [fg.Lane(device=0) for _ in range(2)]
+    for lane, y in zip(lanes, ys):                            # graphs are captured with the lane running alone
+        with lane:
+            net.latent_codec.compress(y)
+    got, errors = [None, None], []
+    gate = threading.Barrier(2)
+
+    def work(k):
+        try:
+            with lanes[k]:
+                gate.wait()
+                for _ in range(3):
+                    enc = net.latent_codec.compress(ys[k])
+                    dec = net.latent_codec.decompress(enc["strings"], enc["shape"])
+                    if not torch.equal(dec["y_hat"], enc["y_hat"]):
+                        errors.append((k, "round trip"))
+                got[k] = enc
+        except Exception as e:                                # noqa: BLE001
+            errors.append((k, repr(e)))
+            gate.abort()
+
+    threads = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+    [t.start() for t in threads]
+    [t.join() for t in threads]
+    assert not errors, errors
+    for k in range(2):
+        assert lanes[k].runner.replays > 0
+        assert torch.equal(got[k]["y_hat"], want[k]["y_hat"])
+        for a, b in zip(got[k]["strings"][:-1], want[k]["strings"][:-1]):
+            assert [x[0] for x in a] == [x[0] for x in b] and [x[1] for x in a] == [x[1] for x in b]
+        assert got[k]["strings"][-1] == want[k]["strings"][-1]
+
+
 # ---- plausible parameters: the synthetic mixture of config 4 in place of the random-init networks' output ----
 from gmm_models import SyntheticMixtures  # noqa: E402
 
