@@ -342,19 +342,34 @@ def run_b200(args):
     W = max(args.warmup, 3)
     # ---- device-resident arm ----
     ctxs = [_lib.ctx(local) if j == 0 else _lib.new_ctx(local) for j in range(depth)]
-    lanes_d = [Lane(batches, ctxs[j]) for j in range(depth)]
-    for ln in lanes_d:
-        for i in range(W if ln is lanes_d[0] else 2):
+    # Several batches in flight, inputs in HBM: the lanes' ctxs are created with FLASHGMM_PUSH=device -- the push warps'
+    # latency (7.2 ms per batch against 2.7 on 15 host workers) hides behind the other lanes' decodes, and D x 15 worker
+    # threads no longer share the 16 cores with the D lane threads (measured, D = 6: 2830-3130 Msym/s against 2500-2800).
+    # One batch in flight, the per-kernel profile, the latency figures and the end-to-end arm keep the default policy
+    # (cost-model split). With several ranks per host the cost model gets there by itself (one worker per ctx).
+    push_device_lanes = world == 1 and depth >= 3 and "FLASHGMM_PUSH" not in os.environ
+    if push_device_lanes:
+        os.environ["FLASHGMM_PUSH"] = "device"
+        try:
+            ctxs_pipe = [_lib.new_ctx(local) for _ in range(depth)]
+        finally:
+            del os.environ["FLASHGMM_PUSH"]
+    else:
+        ctxs_pipe = ctxs
+    lanes_d = [Lane(batches, ctxs_pipe[j]) for j in range(depth)]
+    lanes_1 = [Lane(batches, ctxs[0])] if push_device_lanes else lanes_d[:1]
+    for ln in lanes_d + (lanes_1 if push_device_lanes else []):
+        for i in range(W if ln in (lanes_d[0], lanes_1[0]) else 2):
             outs, streams = ln.step(i)
             check(outs, batches[i % N_SETS])
     bits = sum(s.size for s in streams) * 8 / (nsym * B)
     sampler = start_clock_sampler(local) if rank == 0 else None
     secs, launches = timed(lanes_d, args.steps)
     clocks = stop_clock_sampler(sampler)
-    secs_d1, _ = timed(lanes_d[:1], max(2, args.steps // 2)) if depth > 1 else (secs, 0)
+    secs_d1, _ = timed(lanes_1, max(2, args.steps // 2)) if depth > 1 else (secs, 0)
     steps_d1 = max(2, args.steps // 2) if depth > 1 else args.steps
     # per-kernel CUDA-event timing in a separate pass on one lane (events add host work to every launch)
-    timed(lanes_d[:1], max(2, args.steps // 4), profile=True)
+    timed(lanes_1, max(2, args.steps // 4), profile=True)
     prof = {}
     for kind, name in ((0, "gmm_startfreq"), (1, "gmm_cdf_rows"), (4, "gmm_pop_rows"), (5, "gmm_push")):
         ms, n, by = C.c_double(), C.c_uint64(), C.c_double()
@@ -363,7 +378,7 @@ def run_b200(args):
             prof[name] = dict(ms=ms.value, launches=n.value, bytes=by.value)
 
     # encode-only / decode-only split on the same inputs, one lane (reported beside the headline)
-    ln0 = lanes_d[0]
+    ln0 = lanes_1[0]
     bs = [[x.copy() for x in ln0.encode(k)] for k in range(N_SETS)]
     torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -487,7 +502,10 @@ def run_b200(args):
                    "decode": "device-resident (rows kernel -> pop kernel, one warp per stream)",
                    "encode": "batched startfreq launches -> serial push: the longest streams on host worker threads (records "
                              "come down wave by wave), the rest on the device (push kernel, one warp per stream), "
-                             "split by a cost model (FLASHGMM_PUSH)",
+                             "split by a cost model (FLASHGMM_PUSH)"
+                             + ("; the lanes of `value` (several batches in flight, inputs in HBM) use FLASHGMM_PUSH=device: "
+                                "every stream on the push kernel" if push_device_lanes else ""),
+                   "push_policy_of_value_lanes": "device" if push_device_lanes else "cost model",
                    "host_workers": int(os.environ.get("FLASHGMM_WORKERS", "0")) or min(16, max(1, (os.cpu_count() or 2) - 1)),
                    "host_cores": os.cpu_count(), "cpus_bound_to_gpu_locality": numa_cpus},
         "value_one_batch_in_flight": round(2 * nsym * B * steps_d1 * world / secs_d1 / 1e6, 2),

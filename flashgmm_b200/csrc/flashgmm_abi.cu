@@ -898,6 +898,12 @@ int plan_push_split(const flashgmm_ctx* ctx, const flashgmm_stream* streams, int
     // faster than the link delivers; a device part only adds its push as a tail (measured 14.4 ms
     // split against 12.7 ms all-host for 24 images)
     if (mem == FLASHGMM_MEM_HOST && ctx->n_workers >= 6) return n_streams;
+    // Not lane-aware on purpose. With several ctxs coding at once (one per host thread) the whole batch is better off on
+    // the push kernel -- its latency hides behind the other lanes and the host cores stay free: 6 batches in flight, 16
+    // cores, 2500-2800 Msym/s with this split against 2830-3130 with FLASHGMM_PUSH=device -- but deciding that per call
+    // from the number of other batch calls in flight made lanes flip between the two paths and halved the rate
+    // (1270-1480 Msym/s, measured); the application states it instead (FLASHGMM_PUSH=device when it creates the ctxs of
+    // its lanes: bench.py does).
     const double workers = (double)std::max(1, ctx->n_workers);
     double best = 1e300, host_sum = 0;
     int best_k = n_streams;

@@ -172,6 +172,8 @@ gmm_push_kernel(const PushDesc* __restrict__ descs, const PushRcp* __restrict__ 
 // threads) is draining at that moment -- measured: the push kernel then takes 10.2 ms instead of
 // 2.2 ms. So the stream that issues such wide kernels beside the push kernel first waits, ON THE
 // DEVICE, until every push warp has reported in. Bounded: gives up after `timeout_ns`.
+// (Round 1 and most of round 2. Superseded by the shared-memory reservation below, which needs no inter-kernel
+// progress assumption; kept behind FLASHGMM_PUSH_SPREAD_KB=0.)
 __global__ void gmm_wait_started_kernel(const unsigned int* started, unsigned int target, unsigned long long timeout_ns) {
     if (threadIdx.x != 0) return;
     unsigned long long t0, t;
@@ -185,14 +187,36 @@ __global__ void gmm_wait_started_kernel(const unsigned int* started, unsigned in
 
 }  // namespace
 
+// Spread BY CONSTRUCTION (default): every push CTA reserves FLASHGMM_PUSH_SPREAD_KB (default 40) KB of dynamic shared
+// memory it never touches, so that at most floor(227 / 40) = 5 of them fit on one SM wherever the block scheduler puts
+// them (740 resident on the GPU), and nothing has to wait for anything. Measured with 6 batches in flight and the device
+// push: 2524 Msym/s with the wait kernel below, 3100-3130 with 28 / 40 / 56 KB, 2970-3000 with 75 / 100 KB.
+// FLASHGMM_PUSH_SPREAD_KB=0 restores the wait kernel.
+static int push_spread_bytes() {
+    static const int v = [] {
+        const char* e = getenv("FLASHGMM_PUSH_SPREAD_KB");
+        long kb = e && *e ? strtol(e, nullptr, 10) : 40;
+        if (kb < 0) kb = 0;
+        if (kb > 200) kb = 200;
+        return (int)(kb * 1024);
+    }();
+    return v;
+}
+
 cudaError_t launch_gmm_push(const PushDesc* descs_d, int n_desc, const PushRcp* rcp_d, uint32_t* out,
                             unsigned long long* out_used, unsigned int* started, cudaStream_t st) {
     if (n_desc <= 0) return cudaSuccess;
-    gmm_push_kernel<<<n_desc, 32, 0, st>>>(descs_d, rcp_d, out, out_used, started);
+    const int spread = push_spread_bytes();
+    if (spread > 0) {
+        cudaError_t e = cudaFuncSetAttribute(gmm_push_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, spread);
+        if (e != cudaSuccess) return e;
+    }
+    gmm_push_kernel<<<n_desc, 32, (size_t)spread, st>>>(descs_d, rcp_d, out, out_used, started);
     return cudaGetLastError();
 }
 
 cudaError_t launch_gmm_wait_started(const unsigned int* started, unsigned int target, cudaStream_t st) {
+    if (push_spread_bytes() > 0) return cudaSuccess;          // the push CTAs cannot be packed: nothing to wait for
     gmm_wait_started_kernel<<<1, 32, 0, st>>>(started, target, 3000000ull);      // 3 ms at most
     return cudaGetLastError();
 }
