@@ -10,7 +10,7 @@ from hypothesis import HealthCheck, given, settings, strategies as st  # noqa: E
 from flashgmm_b200 import ans  # noqa: E402
 from oracle import port, ref  # noqa: E402
 
-FAST = dict(deadline=None, suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
+FAST = dict(deadline=None, derandomize=True, database=None, suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
 
 
 # ---- file container ---------------------------------------------------------------------------------------
