@@ -11,6 +11,7 @@ import pytest
 
 from flashgmm_b200 import synth
 from oracle import port, ref
+from helpers import extreme_params
 
 GOLD = Path(__file__).resolve().parent / "golden"
 MD5 = json.loads((GOLD / "gmm_md5.json").read_text())
@@ -126,3 +127,21 @@ def test_phi_is_monotone_on_sampled_windows(mode):
     for t0 in starts:
         bits = struct.unpack("<I", struct.pack("<f", t0))[0]
         assert L.fgo_phi_count_decreasing(C.c_int(mode), C.c_uint32(bits), C.c_uint32(400_000)) == 0, t0
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_port_matches_compiled_reference_on_extreme_parameters(mode, ref_available):
+    if not ref_available:
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    with ref.RefWorker(mode) as wk:
+        for seed in (201, 202, 203):
+            sym, sg, mu, w = extreme_params(seed)
+            R = synth.search_radius(sym)
+            b, _ = wk.gmm_encode(sym, sg, mu, w, R)
+            assert port.gmm_encode(sym, sg, mu, w, mode) == b, seed
+            # the search decoder on the same parameters: oracle == reference symbol for symbol (whether or not the
+            # stream round-trips -- with non-monotone rows the reference itself may not)
+            small = slice(0, 1500)                                      # the reference's search is O(log R) calls per symbol
+            b2, _ = wk.gmm_encode(sym[small], sg[small], mu[small], w[small], R)
+            d, _ = wk.gmm_decode(b2, sg[small], mu[small], w[small], R)
+            assert np.array_equal(port.gmm_decode(b2, sg[small], mu[small], w[small], R, mode), d), seed

@@ -288,3 +288,23 @@ def test_peaky_mixtures_with_saturated_boundaries(pop_ctx, mode):
     assert rc == 0 and not any(status)
     for g, wd in zip(got, want):
         assert np.array_equal(g, wd)
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_parameter_corners_encode_and_decode_like_the_oracle(pop_ctx, mode):
+    """tests/helpers.extreme_params: scales far outside the model's clamp, one-hot / vanishing / unnormalised weights,
+    means on interval boundaries, off-model symbols, a search radius of ~20 000 -- the corners on which the oracle is
+    pinned to the compiled reference in tests/test_oracle.py. Bytes and symbols must be the oracle's."""
+    from flashgmm_b200 import batch
+    from helpers import extreme_params
+    sets = [extreme_params(300 + 10 * mode + k, n=12000) for k in range(2)]
+    want_bytes = [port.gmm_encode(sym, sg, mu, w, mode) for sym, sg, mu, w in sets]
+    streams = [(torch.from_numpy(sym).cuda(), kmajor(sg, "cuda"), kmajor(mu, "cuda"), kmajor(w, "cuda")) for sym, sg, mu, w in sets]
+    got_bytes = batch.encode_batch(streams, mode)
+    assert got_bytes == want_bytes
+    items = [(b, sg, mu, w, synth.search_radius(sym)) for b, (sym, sg, mu, w) in zip(want_bytes, sets)]
+    want = [port.gmm_decode(b, sg, mu, w, R, mode) for b, sg, mu, w, R in items]
+    got, status, rc = decode_batch(pop_ctx(), items, mode)
+    assert rc == 0 and not any(status)
+    for g, wd in zip(got, want):
+        assert np.array_equal(g, wd)
