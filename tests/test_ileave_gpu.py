@@ -144,3 +144,17 @@ def test_parameters_that_are_not_a_mixture_still_roundtrip():
         blob = ileave.encode(s, a, m, ww, 30, mode, 11)
         assert blob == port.ileave_encode(sym, sg, mu, w, 30, mode, 11)
         assert torch.equal(ileave.decode(blob, a, m, ww), s)
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_parameter_corners_roundtrip_and_match_the_cpu_statement(mode):
+    """tests/helpers.extreme_params (scales 1e-4 .. 5000, one-hot / vanishing / unnormalised weights, means on interval
+    boundaries, off-model symbols): wrapped intervals and insane parameters are escaped, the rest is coded -- same bytes
+    as the CPU statement of the format, exact round trip."""
+    from helpers import extreme_params
+    sym, sg, mu, w = extreme_params(400 + mode, n=20000)
+    s, a, m, ww = dev(sym, sg, mu, w)
+    for R in (30, 2000):
+        blob = ileave.encode(s, a, m, ww, R, mode, 12)
+        assert blob == port.ileave_encode(sym, sg, mu, w, R, mode, 12)
+        assert torch.equal(ileave.decode(blob, a, m, ww), s)
