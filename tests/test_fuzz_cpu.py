@@ -123,7 +123,7 @@ def test_table_coder_any_table_matches_the_oracle_and_roundtrips(job):
 
 
 def test_table_coder_values_beyond_the_references_defined_range_roundtrip():
-    """|v - offset| >= 2^27 needs 8 bypass nibbles; the reference's count loop (rans_interface.cpp:370-374) then evaluates
+    """|v - offset| >= 2^27 needs 8 bypass nibbles; the reference's count loop (rans_interface.cpp:377-379) then evaluates
     `raw >> 32` on a 32-bit value (undefined; an endless loop as compiled on x86). The product codes such values with 8
     nibbles and round-trips them -- nothing to compare with."""
     cdfs = np.array([[0, 20000, 40000, 65536, 0, 0]], np.int32)
